@@ -1,0 +1,118 @@
+/* b200ad.h -- C ABI of the B200-native AnimateDiff denoise-step kernels (libb200ad.so).
+ *
+ * Drop-in boundary.  The reference (tanm-ast/video-diffusion-experiments) has no native code: the hot
+ * path is what diffusers/torch execute underneath
+ *     experiments/05_grid_search_ablation.py:158-167   pipe(prompt=..., num_frames=16, ...)
+ *     experiments/03_trace_forward_pass.py:109-113     unet(sample, timestep, encoder_hidden_states=...)
+ * Each entry point below replaces the torch/cuDNN/cuBLAS library kernels one diffusers module reaches
+ * (SURVEY.md section 2.4, K1..K12); the diffusers-shaped Python surface that binds them lives in
+ * video-diffusion-experiments_b200/ and is loaded with ctypes.
+ *
+ * Conventions
+ *  - Plain pointers and sizes only; every pointer is DEVICE memory owned by the caller unless stated.
+ *  - Activations are channels-last: an image batch [N,H,W,C] is the row-major matrix [N*H*W, C];
+ *    frame-images are ordered (batch b, frame f): n = b*F + f.
+ *  - `op_dtype`: 0 = bf16 operands on tcgen05 tensor cores (fast mode), 1 = fp32 operands on SIMT FFMA
+ *    (the "fp32 kernel mode" of the north star).  "operand-typed" buffers hold that type.
+ *  - The residual stream, norm statistics, softmax and all epilogue math are fp32 in both modes.
+ *  - Kernels never allocate and never synchronise; they run on `stream` (a cudaStream_t) and are
+ *    CUDA-graph capturable.  There is no CPU fallback: without a CUDA device every compute call fails.
+ *  - Return 0 on success, <0 on error; b200ad_last_error() returns a thread-local message.
+ */
+#ifndef B200AD_H
+#define B200AD_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* b200ad_last_error(void);
+int b200ad_version(void);
+/* number of kernels launched by this library in this process since load (bench.py "gpu_launches") */
+long long b200ad_launch_count(void);
+
+/* ---- K2: Linear / 1x1 conv (replaces torch.nn.functional.linear / cuBLAS under diffusers
+ * Attention.to_q/k/v/to_out, FeedForward, Transformer2DModel.proj_in/out, ResnetBlock2D.conv_shortcut).
+ *   C[M,N] = A[M,K(lda)] * W[N,K]^T (+bias[N]) (+row_bias[(row/rb_div)*ld_rb + col]) (+residual[M,ld_res])
+ *   writes out_f32[M,ld_o32] and/or out_op[M,ld_oop]; geglu=1: W rows interleaved (h0,g0,h1,g1..) and
+ *   out_op[M,N/2] = (h+bh)*gelu_erf(g+bg)   (diffusers GEGLU). */
+int b200ad_gemm(int op_dtype, const void* A, long long lda, const void* W, int M, int N, int K,
+                const float* bias, const float* row_bias, int rb_div, int ld_rb,
+                const float* residual, long long ld_res, float* out_f32, long long ld_o32,
+                void* out_op, long long ld_oop, int geglu, void* stream);
+
+/* ---- K1: 3x3 convolution as implicit GEMM over NHWC (replaces cuDNN under ResnetBlock2D.conv1/conv2,
+ * Downsample2D.conv, Upsample2D.conv).  src: operand-typed [src_nimg, src_h, src_w, cin]; W: [cout, 9*cin]
+ * with k = (ky*3+kx)*cin + c; output rows = nimg*h*w pixels.  mode 0: stride 1 pad 1 (src geometry = output
+ * geometry).  mode 1: stride 2 pad 1 on a phase-split source produced by b200ad_cast(mode=1)
+ * (src_nimg = 4*nimg, src_h = h, src_w = w). Epilogue arguments as in b200ad_gemm (no geglu). */
+int b200ad_conv3x3(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout,
+                   int mode, const float* bias, const float* row_bias, int rb_div, int ld_rb,
+                   const float* residual, long long ld_res, float* out_f32, long long ld_o32,
+                   void* out_op, long long ld_oop, void* stream);
+
+/* ---- K6: GroupNorm (replaces torch.nn.GroupNorm [+SiLU] in ResnetBlock2D.norm1/2, Transformer2DModel.norm,
+ * AnimateDiffTransformer3D.norm, conv_norm_out).  Input is the channel-concatenation of x0[rows,c0] and
+ * x1[rows,c1] (x1 may be NULL; this is the UNet skip torch.cat), rows = nimg*hw.
+ * stats: float2 partial sums [nimg, nblk, groups]; nblk = b200ad_gn_nblk(hw).  The `partial` workspace must hold
+ * (nimg*nblk*groups + nimg*groups) float2: gn_apply reduces the partials to (mean, rstd) in its tail.  apply: frames_per_stat=1 for
+ * per-frame statistics, =F for the motion module (statistics over all F frames of a batch item).
+ * out_op[rows, c0+c1] = maybe_silu(gn(x)); raw_op (optional) = x cast to the operand type (conv_shortcut input). */
+int b200ad_gn_nblk(int hw);
+int b200ad_gn_stats(const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
+                    float* partial, void* stream);
+int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
+                    const float* partial, int frames_per_stat, float eps, const float* gamma, const float* beta,
+                    int silu, void* out_op, void* raw_op, void* stream);
+
+/* ---- K7: LayerNorm (+ sinusoidal positional-embedding add of the motion module; replaces nn.LayerNorm and
+ * SinusoidalPositionalEmbedding).  x fp32 [rows,C]; pe fp32 [max_seq,C] or NULL; frame index of a row is
+ * (row / hw) % frames. */
+int b200ad_layernorm(int op_dtype, const float* x, int rows, int C, const float* gamma, const float* beta, float eps,
+                     const float* pe, int hw, int frames, void* out_op, void* stream);
+
+/* ---- K9: fp32 -> operand-type copies with re-layout.  mode 0: plain cast [rows*C].  mode 1: space-to-depth
+ * phase split of NHWC [nimg,h,w,C] -> [4*nimg, h/2, w/2, C] (input of a stride-2 conv).  mode 2: nearest x2
+ * upsample NHWC [nimg,h,w,C] -> [nimg,2h,2w,C] (Upsample2D). */
+int b200ad_cast(int op_dtype, const float* x, int nimg, int h, int w, int C, int mode, void* out_op, void* stream);
+
+/* ---- K3/K4: spatial self-attention and text cross-attention (replaces F.scaled_dot_product_attention in
+ * AttnProcessor2_0).  q/k/v: operand-typed, head `hd` of batch item n at q[(n*Lq + i)*ldq + hd*dpad + j];
+ * k/v batch index = n / kv_div (text K/V shared by the frames of a batch item).  dpad >= d is the padded head
+ * width (64/128/192 on the tcgen05 path, pad columns zero); out_op[(n*Lq+i)*ldo + hd*d + j], softmax scale = d^-1/2. */
+int b200ad_attention(int op_dtype, const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                     long long ldv, int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div,
+                     void* out_op, long long ldo, void* stream);
+
+/* ---- K5: motion-module temporal self-attention over the frame axis, read in place from the (b,f,hw)-ordered
+ * rows (no permute copy).  qkv: operand-typed [B*F*hw, 3C] = (q|k|v); out_op [B*F*hw, C]. */
+int b200ad_temporal_attention(int op_dtype, const void* qkv, int B, int F, int hw, int C, int heads,
+                              void* out_op, void* stream);
+
+/* ---- K11: timestep embedding (Timesteps flip_sin_to_cos + small-M Linear with optional SiLU in/out).
+ * small_linear: y[M,N] = act_out(W[N,K] * act_in(x[M,K]) + b), M <= 8, fp32. */
+int b200ad_timestep_sinusoid(const float* t, int B, int dim, float* out, void* stream);
+int b200ad_small_linear(const float* x, int M, int K, const float* W, const float* b, int N, int silu_in,
+                        int silu_out, float* y, void* stream);
+
+/* ---- conv_in (4 -> C0, reads the [B,Cin,F,h,w] latent batch directly) and conv_out (C0 -> 4, writes
+ * [B,Cout,F,h,w]); W in torch layout [cout,cin,3,3] fp32. */
+int b200ad_conv_in(const float* sample, int B, int cin, int F, int h, int w, const float* W, const float* bias,
+                   int cout, float* out_nhwc, void* stream);
+int b200ad_conv_out(int op_dtype, const void* act_nhwc, int B, int F, int h, int w, int cin, const float* W,
+                    const float* bias, int cout, float* out_bcfhw, void* stream);
+
+/* ---- K10 (+K12 tail): classifier-free-guidance combine fused with the scheduler update
+ * (replaces noise_pred.chunk(2) / u+g*(c-u) / DDIMScheduler.step or EulerDiscreteScheduler.step and the next
+ * iteration's torch.cat([latents]*2) + scale_model_input).
+ *   guided = eps_u + g*(eps_c - eps_u);  latents' = cx*latents + ce*guided;
+ *   model_in[0..1] = latents' * in_scale (both CFG halves; may be NULL). */
+int b200ad_cfg_step(const float* eps_u, const float* eps_c, const float* latents, float g, float cx, float ce,
+                    float in_scale, long long n, float* latents_out, float* model_in, int model_in_copies,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200AD_H */

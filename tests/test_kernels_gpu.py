@@ -1,0 +1,253 @@
+"""Kernel-level parity (-m gpu): each C-ABI entry point against a plain PyTorch fp32 reference of the same op
+on identical seeded inputs.  bf16 mode: inputs are made bf16-representable so the only differences are
+accumulation order and the single output rounding; tolerances are written per test.  fp32 mode: <= 1e-5."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def ops(mode):
+    import b200ad.ops as O
+    return O.get_ops(mode)
+
+
+def rnd(*shape, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale)
+
+
+def bf(x):
+    return x.to(torch.bfloat16).float()
+
+
+def rel(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-20)).item()
+
+
+MODES = [("bf16", 6e-3), ("fp32", 2e-5)]
+
+
+@pytest.mark.parametrize("mode,tol", MODES)
+@pytest.mark.parametrize("M,N,K", [(256, 128, 64), (1000, 320, 320), (4096, 1280, 640), (300, 2560, 320),
+                                   (128, 32, 2880), (77, 640, 768)])
+def test_gemm_bias_residual(mode, tol, M, N, K):
+    o = ops(mode)
+    a, w = bf(rnd(M, K, seed=1)), bf(rnd(N, K, seed=2, scale=K ** -0.5))
+    bias, res = rnd(N, seed=3), rnd(M, N, seed=4)
+    ref = a @ w.t() + bias + res
+    out32, outop = o.gemm(a.to(DEV, o.op_dtype), w.to(DEV, o.op_dtype), bias=bias.to(DEV), residual=res.to(DEV),
+                          want_f32=True, want_op=True)
+    assert rel(out32.cpu(), ref) < (1e-5 if mode == "fp32" else 1e-5 + 2e-6)   # fp32 accumulate of exact bf16 products
+    assert rel(outop.cpu(), ref) < tol
+
+
+@pytest.mark.parametrize("mode,tol", MODES)
+def test_gemm_inplace_residual_and_rowbias(mode, tol):
+    o = ops(mode)
+    M, N, K = 512, 320, 320
+    a, w = bf(rnd(M, K, seed=1)), bf(rnd(N, K, seed=2, scale=K ** -0.5))
+    rb = rnd(4, N, seed=5)
+    x = rnd(M, N, seed=6)
+    ref = a @ w.t() + rb.repeat_interleave(M // 4, 0) + x
+    xd = x.to(DEV)
+    o.gemm(a.to(DEV, o.op_dtype), w.to(DEV, o.op_dtype), row_bias=rb.to(DEV), rb_div=M // 4, residual=xd, out_f32=xd)
+    assert rel(xd.cpu(), ref) < 2e-5
+
+
+@pytest.mark.parametrize("mode,tol", MODES)
+def test_gemm_geglu(mode, tol):
+    o = ops(mode)
+    M, C = 384, 320
+    a = bf(rnd(M, C, seed=1))
+    w = bf(rnd(8 * C, C, seed=2, scale=C ** -0.5))
+    b = rnd(8 * C, seed=3)
+    hg = a @ w.t() + b
+    h, g = hg.chunk(2, -1)
+    ref = h * F.gelu(g)
+    wi = torch.stack([w[:4 * C], w[4 * C:]], 1).reshape(8 * C, C).contiguous()
+    bi = torch.stack([b[:4 * C], b[4 * C:]], 1).reshape(8 * C).contiguous()
+    _, out = o.gemm(a.to(DEV, o.op_dtype), wi.to(DEV, o.op_dtype), bias=bi.to(DEV), want_op=True, geglu=True)
+    assert out.shape == (M, 4 * C)
+    assert rel(out.cpu(), ref) < tol
+
+
+def _conv_ref(x_nhwc, w, b, stride=1):
+    y = F.conv2d(x_nhwc.permute(0, 3, 1, 2), w, b, stride=stride, padding=1)
+    return y.permute(0, 2, 3, 1).contiguous()
+
+
+def _pack_conv(w):
+    return w.permute(0, 2, 3, 1).reshape(w.shape[0], -1).contiguous()
+
+
+@pytest.mark.parametrize("mode,tol", MODES)
+@pytest.mark.parametrize("n,h,w,cin,cout", [(2, 64, 64, 64, 64), (3, 32, 32, 128, 320), (5, 16, 16, 320, 64),
+                                            (6, 8, 8, 64, 128), (9, 4, 4, 64, 64), (2, 12, 12, 64, 64),
+                                            (1, 24, 40, 64, 96)])
+def test_conv3x3(mode, tol, n, h, w, cin, cout):
+    o = ops(mode)
+    x = bf(rnd(n, h, w, cin, seed=1))
+    wt = bf(rnd(cout, cin, 3, 3, seed=2, scale=(9 * cin) ** -0.5))
+    b = rnd(cout, seed=3)
+    temb = rnd(n, cout, seed=4)
+    ref = _conv_ref(x, wt, b) + temb[:, None, None, :]
+    out, _ = o.conv3x3(x.to(DEV, o.op_dtype), _pack_conv(wt).to(DEV, o.op_dtype), n, h, w, bias=b.to(DEV),
+                       row_bias=temb.to(DEV), rb_div=h * w)
+    assert rel(out.cpu().view(n, h, w, cout), ref) < 2e-5
+
+
+@pytest.mark.parametrize("mode,tol", MODES)
+@pytest.mark.parametrize("n,h,w,c", [(2, 32, 32, 64), (3, 8, 8, 128), (1, 64, 64, 64)])
+def test_conv3x3_stride2_and_upsample(mode, tol, n, h, w, c):
+    o = ops(mode)
+    x = bf(rnd(n, h, w, c, seed=1))
+    wt = bf(rnd(c, c, 3, 3, seed=2, scale=(9 * c) ** -0.5))
+    b = rnd(c, seed=3)
+    xd = x.to(DEV)
+    # Downsample2D: conv stride 2 pad 1
+    ref = _conv_ref(x, wt, b, stride=2)
+    s2d = o.cast(xd, n, h, w, c, mode=1)
+    out, _ = o.conv3x3(s2d, _pack_conv(wt).to(DEV, o.op_dtype), n, h // 2, w // 2, stride2=True, bias=b.to(DEV))
+    assert rel(out.cpu().view(n, h // 2, w // 2, c), ref) < 2e-5
+    # Upsample2D: nearest x2 then conv
+    up = F.interpolate(x.permute(0, 3, 1, 2), scale_factor=2.0, mode="nearest").permute(0, 2, 3, 1).contiguous()
+    ref = _conv_ref(up, wt, b)
+    upd = o.cast(xd, n, h, w, c, mode=2)
+    out, _ = o.conv3x3(upd, _pack_conv(wt).to(DEV, o.op_dtype), n, 2 * h, 2 * w, bias=b.to(DEV))
+    assert rel(out.cpu().view(n, 2 * h, 2 * w, c), ref) < 2e-5
+
+
+@pytest.mark.parametrize("mode,tol", MODES)
+@pytest.mark.parametrize("nimg,hw,c0,c1,fps,silu", [(4, 256, 320, 0, 1, True), (4, 64, 1280, 640, 1, True),
+                                                    (8, 1024, 640, 320, 1, True), (8, 100, 320, 0, 4, False),
+                                                    (2, 4096, 64, 0, 2, False), (3, 16, 2560, 0, 1, True)])
+def test_group_norm(mode, tol, nimg, hw, c0, c1, fps, silu):
+    o = ops(mode)
+    x0 = rnd(nimg * hw, c0, seed=1) * 2 + 0.5
+    x1 = rnd(nimg * hw, c1, seed=2) if c1 else None
+    C = c0 + c1
+    gamma, beta = rnd(C, seed=3), rnd(C, seed=4)
+    x = x0 if x1 is None else torch.cat([x0, x1], -1)
+    xr = x.view(nimg // fps, fps * hw, C).permute(0, 2, 1)           # [stat, C, fps*hw]
+    ref = F.group_norm(xr, 32, gamma, beta, eps=1e-6).permute(0, 2, 1).reshape(nimg * hw, C)
+    if silu:
+        ref = F.silu(ref)
+    out, raw = o.group_norm(x0.to(DEV), None if x1 is None else x1.to(DEV), nimg, hw, 32, gamma.to(DEV),
+                            beta.to(DEV), 1e-6, silu=silu, frames_per_stat=fps, want_raw=True)
+    assert rel(out.cpu(), ref) < (4e-3 if mode == "bf16" else 1e-5)
+    assert rel(raw.cpu(), x) < (4e-3 if mode == "bf16" else 1e-7)
+
+
+@pytest.mark.parametrize("mode,tol", MODES)
+@pytest.mark.parametrize("rows,C,pe", [(1000, 320, False), (2 * 4 * 50, 640, True), (333, 1280, True), (64, 64, False)])
+def test_layer_norm(mode, tol, rows, C, pe):
+    o = ops(mode)
+    x = rnd(rows, C, seed=1) * 3 + 1
+    gamma, beta = rnd(C, seed=2), rnd(C, seed=3)
+    ref = F.layer_norm(x, (C,), gamma, beta, 1e-5)
+    hw, frames = 1, 1
+    ped = None
+    if pe:
+        frames, hw = 4, 50 if rows == 400 else 1
+        if rows == 333:
+            frames, hw = 32, 3
+        table = rnd(32, C, seed=4)
+        f_idx = (torch.arange(rows) // hw) % frames
+        ref = ref + table[f_idx]
+        ped = table.to(DEV)
+    out = o.layer_norm(x.to(DEV), gamma.to(DEV), beta.to(DEV), 1e-5, pe=ped, hw=hw, frames=frames)
+    assert rel(out.cpu(), ref) < (4e-3 if mode == "bf16" else 1e-5)
+
+
+def _attn_ref(q, k, v):
+    return F.scaled_dot_product_attention(q, k, v)
+
+
+@pytest.mark.parametrize("mode,tol", [("bf16", 8e-3), ("fp32", 2e-5)])
+@pytest.mark.parametrize("nb,heads,Lq,Lk,d,dpad,kv_div", [
+    (2, 8, 256, 256, 40, 64, 1), (3, 2, 1024, 1024, 40, 64, 1), (2, 8, 64, 64, 160, 192, 1),
+    (2, 4, 256, 256, 80, 128, 1), (4, 8, 256, 77, 40, 64, 2), (2, 8, 64, 77, 160, 192, 2),
+    (1, 2, 200, 300, 8, 64, 1), (2, 8, 1024, 77, 80, 128, 1)])
+def test_attention(mode, tol, nb, heads, Lq, Lk, d, dpad, kv_div):
+    o = ops(mode)
+    nkv = nb // kv_div
+    q = bf(rnd(nb, heads, Lq, d, seed=1))
+    k = bf(rnd(nkv, heads, Lk, d, seed=2))
+    v = bf(rnd(nkv, heads, Lk, d, seed=3))
+    ref = _attn_ref(q, k.repeat_interleave(kv_div, 0), v.repeat_interleave(kv_div, 0))   # [nb, heads, Lq, d]
+    ref = ref.permute(0, 2, 1, 3).reshape(nb * Lq, heads * d)
+
+    def pack(t, L, n):   # [n, heads, L, d] -> [n*L, heads*dpad] zero padded
+        p = torch.zeros(n, L, heads, dpad)
+        p[..., :d] = t.permute(0, 2, 1, 3)
+        return p.reshape(n * L, heads * dpad)
+
+    qd = pack(q, Lq, nb).to(DEV, o.op_dtype)
+    kvd = torch.cat([pack(k, Lk, nkv), pack(v, Lk, nkv)], -1).to(DEV, o.op_dtype)   # fused (k|v) buffer
+    out = o.attention(qd, kvd[:, :heads * dpad], kvd[:, heads * dpad:], nb, heads, Lq, Lk, d, dpad, kv_div)
+    assert rel(out.cpu(), ref) < tol
+
+
+@pytest.mark.parametrize("mode,tol", MODES)
+@pytest.mark.parametrize("B,Fr,hw,C,heads", [(2, 16, 64, 320, 8), (1, 16, 16, 1280, 8), (2, 8, 9, 640, 8),
+                                             (1, 32, 4, 1280, 8), (2, 4, 16, 64, 8)])
+def test_temporal_attention(mode, tol, B, Fr, hw, C, heads):
+    o = ops(mode)
+    d = C // heads
+    qkv = bf(rnd(B * Fr * hw, 3 * C, seed=1))
+    t = qkv.view(B, Fr, hw, 3, heads, d).permute(3, 0, 2, 4, 1, 5)       # [3, B, hw, heads, F, d]
+    ref = _attn_ref(t[0], t[1], t[2])                                      # [B, hw, heads, F, d]
+    ref = ref.permute(0, 3, 1, 2, 4).reshape(B * Fr * hw, C)
+    out = o.temporal_attention(qkv.to(DEV, o.op_dtype), B, Fr, hw, C, heads)
+    assert rel(out.cpu(), ref) < (5e-3 if mode == "bf16" else 1e-5)
+
+
+def test_small_ops():
+    o = ops("fp32")
+    t = torch.tensor([961.0, 1.0, 500.5])
+    half = 160
+    freqs = torch.exp(-math.log(10000.0) * torch.arange(half, dtype=torch.float32) / half)
+    e = t[:, None] * freqs[None]
+    ref = torch.cat([torch.cos(e), torch.sin(e)], -1)
+    out = o.timestep_sinusoid(t.to(DEV), 320)
+    assert (out.cpu() - ref).abs().max() < 2e-4      # fp32 sin/cos of arguments up to ~1e3
+    x, w, b = rnd(3, 320, seed=1), rnd(1280, 320, seed=2, scale=0.05), rnd(1280, seed=3)
+    ref = F.silu(F.linear(F.silu(x), w, b))
+    out = o.small_linear(x.to(DEV), w.to(DEV), b.to(DEV), silu_in=True, silu_out=True)
+    assert rel(out.cpu(), ref) < 1e-5
+
+
+@pytest.mark.parametrize("mode,tol", MODES)
+def test_conv_in_out(mode, tol):
+    o = ops(mode)
+    B, Fr, h, w = 2, 3, 16, 12
+    s = rnd(B, 4, Fr, h, w, seed=1)
+    wi, bi = rnd(320, 4, 3, 3, seed=2, scale=0.2), rnd(320, seed=3)
+    x = s.permute(0, 2, 1, 3, 4).reshape(B * Fr, 4, h, w)
+    ref = F.conv2d(x, wi, bi, padding=1).permute(0, 2, 3, 1).reshape(B * Fr * h * w, 320)
+    out = o.conv_in(s.to(DEV), wi.to(DEV), bi.to(DEV))
+    assert rel(out.cpu(), ref) < 1e-5
+    act = bf(rnd(B * Fr, h, w, 320, seed=4))
+    wo, bo = rnd(4, 320, 3, 3, seed=5, scale=0.02), rnd(4, seed=6)
+    y = F.conv2d(act.permute(0, 3, 1, 2), wo, bo, padding=1)             # [B*F, 4, h, w]
+    ref = y.view(B, Fr, 4, h, w).permute(0, 2, 1, 3, 4)
+    out = o.conv_out(act.to(DEV, o.op_dtype).view(-1, 320), B, Fr, h, w, wo.to(DEV), bo.to(DEV))
+    assert rel(out.cpu(), ref) < 1e-5
+
+
+def test_cfg_step_matches_formula():
+    o = ops("fp32")
+    n = 4 * 16 * 64 * 64
+    u, c, x = rnd(n, seed=1), rnd(n, seed=2), rnd(n, seed=3)
+    g, cx, ce = 7.5, 1.0173, -0.2231
+    ref = cx * x + ce * (u + g * (c - u))
+    mi = torch.empty(2, n, device=DEV)
+    out = o.cfg_step(u.to(DEV), c.to(DEV), x.to(DEV), g, cx, ce, in_scale=0.5, model_in=mi)
+    assert (out.cpu() - ref).abs().max() < 1e-5
+    assert torch.equal(mi[0], mi[1]) and (mi[0].cpu() - 0.5 * ref).abs().max() < 1e-5

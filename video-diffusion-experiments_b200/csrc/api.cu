@@ -1,0 +1,128 @@
+// C-ABI glue: error reporting, launch accounting, driver entry point lookup, and the GEMM / conv entry
+// points that build GemmArgs and dispatch on the operand dtype (bf16 -> tcgen05, fp32 -> SIMT).
+#include <atomic>
+#include <stdarg.h>
+
+#include "../../include/b200ad.h"
+#include "gemm.cuh"
+#include "tmap.cuh"
+
+namespace b200ad {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+EncodeTiledFn get_encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+static void fill_epilogue(Epilogue& e, const float* bias, const float* row_bias, int rb_div, int ld_rb,
+                          const float* residual, long long ld_res, float* out_f32, long long ld_o32, void* out_op,
+                          long long ld_oop, int geglu) {
+  e.bias = bias;
+  e.row_bias = row_bias;
+  e.rb_div = rb_div > 0 ? rb_div : 1;
+  e.ld_rb = ld_rb;
+  e.residual = residual;
+  e.ld_res = ld_res;
+  e.out_f32 = out_f32;
+  e.ld_o32 = ld_o32;
+  e.out_op = out_op;
+  e.ld_oop = ld_oop;
+  e.geglu = geglu;
+}
+
+}  // namespace b200ad
+
+using namespace b200ad;
+
+extern "C" {
+
+const char* b200ad_last_error(void) { return g_err; }
+int b200ad_version(void) { return 100; }
+long long b200ad_launch_count(void) { return g_launches.load(); }
+
+int b200ad_gemm(int op_dtype, const void* A, long long lda, const void* W, int M, int N, int K, const float* bias,
+                const float* row_bias, int rb_div, int ld_rb, const float* residual, long long ld_res,
+                float* out_f32, long long ld_o32, void* out_op, long long ld_oop, int geglu, void* stream) {
+  B200AD_REQUIRE(A && W, "gemm: null operand");
+  B200AD_REQUIRE(out_f32 || out_op, "gemm: no output buffer");
+  GemmArgs a;
+  memset(&a, 0, sizeof(a));
+  a.A = A; a.lda = lda; a.W = W; a.M = M; a.N = N; a.K = K;
+  fill_epilogue(a.epi, bias, row_bias, rb_div, ld_rb, residual, ld_res, out_f32, ld_o32, out_op, ld_oop, geglu);
+  if (op_dtype == 0) return gemm_bf16_tc(a, (cudaStream_t)stream);
+  if (op_dtype == 1) return gemm_f32_simt(a, (cudaStream_t)stream);
+  set_error("gemm: unknown op_dtype %d", op_dtype);
+  return -1;
+}
+
+int b200ad_conv3x3(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout, int mode,
+                   const float* bias, const float* row_bias, int rb_div, int ld_rb, const float* residual,
+                   long long ld_res, float* out_f32, long long ld_o32, void* out_op, long long ld_oop,
+                   void* stream) {
+  B200AD_REQUIRE(src && W, "conv3x3: null operand");
+  B200AD_REQUIRE(out_f32 || out_op, "conv3x3: no output buffer");
+  B200AD_REQUIRE(mode == 0 || mode == 1, "conv3x3: mode %d", mode);
+  GemmArgs a;
+  memset(&a, 0, sizeof(a));
+  a.A = src; a.W = W;
+  a.M = nimg * h * w; a.N = cout; a.K = 9 * cin;
+  ConvGeom& g = a.conv;
+  g.enabled = 1;
+  g.nimg = nimg; g.h = h; g.w = w; g.cin = cin; g.ntaps = 9;
+  g.src_h = h; g.src_w = w;
+  g.src_nimg = mode == 0 ? nimg : 4 * nimg;
+  for (int ky = 0; ky < 3; ++ky)
+    for (int kx = 0; kx < 3; ++kx) {
+      const int t = ky * 3 + kx;
+      if (mode == 0) {
+        g.tap_dy[t] = ky - 1; g.tap_dx[t] = kx - 1; g.tap_dn[t] = 0;
+      } else {
+        // input pixel (2y+ky-1, 2x+kx-1): ky=0 -> odd phase row y-1; ky=1 -> even phase row y; ky=2 -> odd phase row y
+        const int py = (ky == 1) ? 0 : 1, px = (kx == 1) ? 0 : 1;
+        g.tap_dy[t] = (ky == 0) ? -1 : 0;
+        g.tap_dx[t] = (kx == 0) ? -1 : 0;
+        g.tap_dn[t] = (py * 2 + px) * nimg;
+      }
+    }
+  // M tile = 128 output pixels = n_box * h_box * w_box (powers of two)
+  auto best_box = [](int extent, int limit) {
+    int best = 1;
+    double best_eff = -1.0;
+    for (int b = limit; b >= 1; b >>= 1) {
+      const double eff = (double)extent / (double)(((extent + b - 1) / b) * b);
+      if (eff > best_eff + 1e-9) { best_eff = eff; best = b; }
+    }
+    return best;
+  };
+  const int wb = best_box(w, 128);
+  const int hb = best_box(h, 128 / wb);
+  const int nb = 128 / (wb * hb);
+  g.w_box = wb; g.h_box = hb; g.n_box = nb;
+  fill_epilogue(a.epi, bias, row_bias, rb_div, ld_rb, residual, ld_res, out_f32, ld_o32, out_op, ld_oop, 0);
+  if (op_dtype == 0) return gemm_bf16_tc(a, (cudaStream_t)stream);
+  if (op_dtype == 1) return gemm_f32_simt(a, (cudaStream_t)stream);
+  set_error("conv3x3: unknown op_dtype %d", op_dtype);
+  return -1;
+}
+
+}  // extern "C"

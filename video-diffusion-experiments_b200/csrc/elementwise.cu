@@ -1,0 +1,190 @@
+// Memory-bound kernels of the denoise step: GroupNorm statistics / apply (+SiLU, + skip concat), LayerNorm
+// (+positional embedding), re-layout casts, timestep embedding, conv_in / conv_out, CFG + scheduler update.
+// All are coalesced, vectorised where channel grouping allows, with fp32 math; outputs that feed a
+// contraction are written in the operand type T (bf16 fast mode, float in the fp32 kernel mode).
+#include "../../include/b200ad.h"
+#include "ops_common.cuh"
+
+namespace b200ad {
+
+// ----------------------------------------------------------------------------- GroupNorm
+// Thread <-> channel-pair mapping is fixed for a whole block (pairs tid + j*T), so every thread keeps its
+// group's statistics / affine parameters in registers while the block walks over its rows.
+static constexpr int GN_ROWS_PER_BLOCK = 32;
+static constexpr int GN_MAX_PPT = 2;       // channel pairs per thread (C <= 4096)
+
+__host__ __device__ inline int gn_nblk(int hw) { return (hw + GN_ROWS_PER_BLOCK - 1) / GN_ROWS_PER_BLOCK; }
+
+__device__ __forceinline__ float2 gn_load_pair(const float* x0, int c0, const float* x1, int c1, long long row,
+                                               int c) {
+  return (c < c0) ? *reinterpret_cast<const float2*>(x0 + row * c0 + c)
+                  : *reinterpret_cast<const float2*>(x1 + row * c1 + (c - c0));
+}
+
+__global__ void gn_stats_kernel(const float* __restrict__ x0, int c0, const float* __restrict__ x1, int c1, int hw,
+                                int groups, float2* __restrict__ partial) {
+  extern __shared__ float2 sh[];          // [npairs]
+  const int C = c0 + c1;
+  const int npairs = C >> 1;
+  const int cpg = C / groups;
+  const int n = blockIdx.y;
+  const int blk = blockIdx.x;
+  const int r0 = blk * GN_ROWS_PER_BLOCK;
+  const int r1 = min(hw, r0 + GN_ROWS_PER_BLOCK);
+  const int T = blockDim.x;
+#pragma unroll
+  for (int j = 0; j < GN_MAX_PPT; ++j) {
+    const int pr = threadIdx.x + j * T;
+    if (pr < npairs) {
+      float s = 0.f, q = 0.f;
+      const int c = pr * 2;
+#pragma unroll 4
+      for (int r = r0; r < r1; ++r) {
+        float2 v = gn_load_pair(x0, c0, x1, c1, (long long)n * hw + r, c);
+        s += v.x + v.y;
+        q += v.x * v.x + v.y * v.y;
+      }
+      sh[pr] = make_float2(s, q);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < groups) {
+    const int g = threadIdx.x;
+    const int p0 = g * cpg / 2, p1 = (g + 1) * cpg / 2;
+    float s = 0.f, q = 0.f;
+    for (int pr = p0; pr < p1; ++pr) { s += sh[pr].x; q += sh[pr].y; }
+    partial[((long long)n * gridDim.x + blk) * groups + g] = make_float2(s, q);
+  }
+}
+
+// One warp per (statistic index, group): deterministic fp64 reduction of the per-block partial sums.
+__global__ void gn_finalize_kernel(const float2* __restrict__ partial, int nblk, int frames_per_stat, int groups,
+                                   int hw, int cpg, float eps, float2* __restrict__ meanrstd, int nstat) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= nstat * groups) return;
+  const int st = warp / groups, g = warp % groups;
+  const int total = frames_per_stat * nblk;
+  const float2* base = partial + (long long)st * total * groups + g;
+  double s = 0.0, q = 0.0;
+  for (int i = lane; i < total; i += 32) {
+    float2 v = base[(long long)i * groups];
+    s += v.x; q += v.y;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) {
+    const double cnt = (double)frames_per_stat * hw * cpg;
+    const double mean = s / cnt;
+    double var = q / cnt - mean * mean;
+    if (var < 0.0) var = 0.0;
+    meanrstd[warp] = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)eps)));
+  }
+}
+
+template <typename T>
+__global__ void gn_apply_kernel(const float* __restrict__ x0, int c0, const float* __restrict__ x1, int c1, int hw,
+                                int groups, const float2* __restrict__ meanrstd, int frames_per_stat,
+                                const float* __restrict__ gamma, const float* __restrict__ beta, int silu,
+                                T* __restrict__ out, T* __restrict__ raw) {
+  __shared__ float s_mean[64], s_rstd[64];
+  const int C = c0 + c1;
+  const int npairs = C >> 1;
+  const int cpg = C / groups;
+  const int n = blockIdx.y;
+  const int blk = blockIdx.x;
+  if (threadIdx.x < groups) {
+    float2 mr = meanrstd[(n / frames_per_stat) * groups + threadIdx.x];
+    s_mean[threadIdx.x] = mr.x;
+    s_rstd[threadIdx.x] = mr.y;
+  }
+  __syncthreads();
+  const int r0 = blk * GN_ROWS_PER_BLOCK;
+  const int r1 = min(hw, r0 + GN_ROWS_PER_BLOCK);
+  const int T_ = blockDim.x;
+#pragma unroll
+  for (int j = 0; j < GN_MAX_PPT; ++j) {
+    const int pr = threadIdx.x + j * T_;
+    if (pr < npairs) {
+      const int c = pr * 2;
+      const int g = c / cpg;
+      const float mean = s_mean[g], rstd = s_rstd[g];
+      const float ga = gamma[c] * rstd, gb = gamma[c + 1] * rstd;
+      const float ba = beta[c] - mean * ga, bb = beta[c + 1] - mean * gb;
+#pragma unroll 4
+      for (int r = r0; r < r1; ++r) {
+        const long long row = (long long)n * hw + r;
+        float2 v = gn_load_pair(x0, c0, x1, c1, row, c);
+        float a = v.x * ga + ba, b = v.y * gb + bb;
+        if (silu) { a = silu_f(a); b = silu_f(b); }
+        store2<T>(out + row * C + c, a, b);
+        if (raw) store2<T>(raw + row * C + c, v.x, v.y);
+      }
+    }
+  }
+}
+
+static int gn_threads(int C) {
+  const int npairs = C / 2;
+  int t = (npairs + GN_MAX_PPT - 1) / GN_MAX_PPT;
+  if (npairs <= 1024) t = npairs;
+  t = (t + 31) / 32 * 32;
+  return t < 64 ? 64 : t;
+}
+
+}  // namespace b200ad
+
+using namespace b200ad;
+
+extern "C" int b200ad_gn_nblk(int hw) { return gn_nblk(hw); }
+
+extern "C" int b200ad_gn_stats(const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
+                               float* partial, void* stream) {
+  if (!x1) c1 = 0;
+  const int C = c0 + c1;
+  B200AD_REQUIRE(groups <= 64 && C % groups == 0 && (C / groups) % 2 == 0 && c0 % 2 == 0,
+                 "gn_stats: unsupported channels C=%d (c0=%d) groups=%d", C, c0, groups);
+  B200AD_REQUIRE(C / 2 <= 1024 * GN_MAX_PPT, "gn_stats: C=%d too large", C);
+  dim3 grid(gn_nblk(hw), nimg);
+  gn_stats_kernel<<<grid, gn_threads(C), (C / 2) * sizeof(float2), (cudaStream_t)stream>>>(
+      x0, c0, x1, c1, hw, groups, reinterpret_cast<float2*>(partial));
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
+                               int groups, const float* partial, int frames_per_stat, float eps, const float* gamma,
+                               const float* beta, int silu, void* out_op, void* raw_op, void* stream) {
+  if (!x1) c1 = 0;
+  const int C = c0 + c1;
+  B200AD_REQUIRE(groups <= 64 && C % groups == 0 && (C / groups) % 2 == 0 && c0 % 2 == 0,
+                 "gn_apply: unsupported channels C=%d (c0=%d) groups=%d", C, c0, groups);
+  B200AD_REQUIRE(frames_per_stat >= 1 && nimg % frames_per_stat == 0, "gn_apply: nimg=%d frames_per_stat=%d", nimg,
+                 frames_per_stat);
+  dim3 grid(gn_nblk(hw), nimg);
+  const int nblk = gn_nblk(hw);
+  const int nstat = nimg / frames_per_stat;
+  // mean / rstd live in the tail of the caller's `partial` buffer (see b200ad.h)
+  float2* part = reinterpret_cast<float2*>(const_cast<float*>(partial));
+  float2* meanrstd = part + (long long)nimg * nblk * groups;
+  {
+    const int warps = nstat * groups;
+    const int threads = 256;
+    gn_finalize_kernel<<<(warps * 32 + threads - 1) / threads, threads, 0, (cudaStream_t)stream>>>(
+        part, nblk, frames_per_stat, groups, hw, C / groups, eps, meanrstd, nstat);
+    count_launch();
+  }
+  if (op_dtype == 0)
+    gn_apply_kernel<bf16><<<grid, gn_threads(C), 0, (cudaStream_t)stream>>>(
+        x0, c0, x1, c1, hw, groups, meanrstd, frames_per_stat, gamma, beta, silu, (bf16*)out_op, (bf16*)raw_op);
+  else
+    gn_apply_kernel<float><<<grid, gn_threads(C), 0, (cudaStream_t)stream>>>(
+        x0, c0, x1, c1, hw, groups, meanrstd, frames_per_stat, gamma, beta, silu, (float*)out_op, (float*)raw_op);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,234 @@
+// Small kernels at the edges of the UNet: timestep sinusoid, small-M Linear (time MLP, temb projections),
+// conv_in (4 -> C0 straight from the [B,C,F,h,w] latents), conv_out (C0 -> 4 back to [B,C,F,h,w]) and the
+// fused classifier-free-guidance + scheduler update.
+#include "../../include/b200ad.h"
+#include "ops_common.cuh"
+
+namespace b200ad {
+
+// Timesteps(flip_sin_to_cos=True, freq_shift=0): out[b] = [cos(t*f_i) | sin(t*f_i)], f_i = exp(-ln(1e4)*i/half)
+__global__ void timestep_sinusoid_kernel(const float* __restrict__ t, int B, int dim, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int half = dim >> 1;
+  if (i >= B * half) return;
+  const int b = i / half, k = i % half;
+  const float freq = expf(-9.210340371976184f * (float)k / (float)half);
+  const float e = t[b] * freq;
+  out[b * dim + k] = cosf(e);
+  out[b * dim + half + k] = sinf(e);
+}
+
+// y[M,N] = act_out(W[N,K] x[M,K]^T + b); one warp per output column, M <= 8 rows kept in registers.
+__global__ void small_linear_kernel(const float* __restrict__ x, int M, int K, const float* __restrict__ W,
+                                    const float* __restrict__ bias, int N, int silu_in, int silu_out,
+                                    float* __restrict__ y) {
+  const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (n >= N) return;
+  float acc[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) acc[m] = 0.f;
+  const float* wr = W + (long long)n * K;
+  for (int k = lane * 4; k < K; k += 128) {
+    const float4 w4 = *reinterpret_cast<const float4*>(wr + k);
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      if (m < M) {
+        float4 x4 = *reinterpret_cast<const float4*>(x + (long long)m * K + k);
+        if (silu_in) { x4.x = silu_f(x4.x); x4.y = silu_f(x4.y); x4.z = silu_f(x4.z); x4.w = silu_f(x4.w); }
+        acc[m] += w4.x * x4.x + w4.y * x4.y + w4.z * x4.z + w4.w * x4.w;
+      }
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    if (m < M) {
+      float v = warp_sum(acc[m]);
+      if (lane == 0) {
+        v += bias ? bias[n] : 0.f;
+        if (silu_out) v = silu_f(v);
+        y[(long long)m * N + n] = v;
+      }
+    }
+  }
+}
+
+// conv_in: 3x3, pad 1, tiny cin.  Block = PIX consecutive output pixels of one frame-image x all cout
+// (thread = cout, weights for that cout in registers, input patch shared through smem).
+static constexpr int CIN_PIX = 16;
+static constexpr int CIN_MAXK = 72;     // cin*9 <= 72 (cin <= 8)
+__global__ void conv_in_kernel(const float* __restrict__ sample, int B, int cin, int F, int h, int w,
+                               const float* __restrict__ W, const float* __restrict__ bias, int cout,
+                               float* __restrict__ out) {
+  __shared__ float patch[CIN_PIX][CIN_MAXK];
+  const int kk = cin * 9;
+  const long long pix0 = (long long)blockIdx.x * CIN_PIX;
+  const long long npix = (long long)B * F * h * w;
+  for (int i = threadIdx.x; i < CIN_PIX * kk; i += blockDim.x) {
+    const int p = i / kk, k = i % kk;
+    const long long pix = pix0 + p;
+    float v = 0.f;
+    if (pix < npix) {
+      const int x = (int)(pix % w), y = (int)((pix / w) % h);
+      const int n = (int)(pix / ((long long)w * h));
+      const int b = n / F, f = n % F;
+      const int c = k / 9, ky = (k % 9) / 3, kx = k % 3;
+      const int yy = y + ky - 1, xx = x + kx - 1;
+      if (yy >= 0 && yy < h && xx >= 0 && xx < w)
+        v = sample[((((long long)b * cin + c) * F + f) * h + yy) * w + xx];
+    }
+    patch[p][k] = v;
+  }
+  __syncthreads();
+  for (int co = threadIdx.x; co < cout; co += blockDim.x) {
+    float wreg[CIN_MAXK];
+#pragma unroll
+    for (int k = 0; k < CIN_MAXK; ++k) wreg[k] = (k < kk) ? W[(long long)co * kk + k] : 0.f;
+    const float bv = bias ? bias[co] : 0.f;
+    for (int p = 0; p < CIN_PIX; ++p) {
+      if (pix0 + p >= npix) break;
+      float acc = bv;
+#pragma unroll
+      for (int k = 0; k < CIN_MAXK; ++k)
+        if (k < kk) acc += wreg[k] * patch[p][k];
+      out[(pix0 + p) * cout + co] = acc;
+    }
+  }
+}
+
+// conv_out: 3x3, pad 1, tiny cout (<= 4).  One warp per output pixel; lanes split the channel axis.
+template <typename T>
+__global__ void conv_out_kernel(const T* __restrict__ act, int B, int F, int h, int w, int cin,
+                                const float* __restrict__ W, const float* __restrict__ bias, int cout,
+                                float* __restrict__ out) {
+  extern __shared__ float wsm[];          // [cout][9][cin]  (re-ordered from torch [cout][cin][3][3])
+  for (int i = threadIdx.x; i < cout * 9 * cin; i += blockDim.x) {
+    const int c = i % cin, t = (i / cin) % 9, co = i / (9 * cin);
+    wsm[i] = W[((long long)co * cin + c) * 9 + t];
+  }
+  __syncthreads();
+  const long long npix = (long long)B * F * h * w;
+  const long long pix = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (pix >= npix) return;
+  const int x = (int)(pix % w), y = (int)((pix / w) % h);
+  const int n = (int)(pix / ((long long)w * h));
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int t = 0; t < 9; ++t) {
+    const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
+    if (yy < 0 || yy >= h || xx < 0 || xx >= w) continue;
+    const T* ar = act + (((long long)n * h + yy) * w + xx) * cin;
+    for (int c = lane * 2; c < cin; c += 64) {
+      const float2 a = load2<T>(ar + c);
+#pragma unroll
+      for (int co = 0; co < 4; ++co) {
+        if (co < cout) {
+          const float* wr = wsm + ((long long)co * 9 + t) * cin + c;
+          acc[co] += a.x * wr[0] + a.y * wr[1];
+        }
+      }
+    }
+  }
+  const int b = n / F, f = n % F;
+#pragma unroll
+  for (int co = 0; co < 4; ++co) {
+    if (co < cout) {
+      const float v = warp_sum(acc[co]);
+      if (lane == 0) out[((((long long)b * cout + co) * F + f) * h + y) * w + x] = v + (bias ? bias[co] : 0.f);
+    }
+  }
+}
+
+// guided = u + g*(c-u); x' = cx*x + ce*guided; model_in[k] = x'*in_scale for k < copies
+__global__ void cfg_step_kernel(const float4* __restrict__ eu, const float4* __restrict__ ec,
+                                const float4* __restrict__ lat, float g, float cx, float ce, float in_scale,
+                                long long n4, float4* __restrict__ lat_out, float4* __restrict__ model_in,
+                                int copies) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  const float4 u = eu[i], c = ec[i], x = lat[i];
+  float4 r;
+  r.x = cx * x.x + ce * (u.x + g * (c.x - u.x));
+  r.y = cx * x.y + ce * (u.y + g * (c.y - u.y));
+  r.z = cx * x.z + ce * (u.z + g * (c.z - u.z));
+  r.w = cx * x.w + ce * (u.w + g * (c.w - u.w));
+  lat_out[i] = r;
+  if (model_in) {
+    const float4 s = make_float4(r.x * in_scale, r.y * in_scale, r.z * in_scale, r.w * in_scale);
+    for (int k = 0; k < copies; ++k) model_in[(long long)k * n4 + i] = s;
+  }
+}
+
+}  // namespace b200ad
+
+using namespace b200ad;
+
+extern "C" int b200ad_timestep_sinusoid(const float* t, int B, int dim, float* out, void* stream) {
+  B200AD_REQUIRE(dim % 2 == 0, "timestep_sinusoid: dim=%d", dim);
+  const int total = B * dim / 2;
+  timestep_sinusoid_kernel<<<(total + 127) / 128, 128, 0, (cudaStream_t)stream>>>(t, B, dim, out);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200ad_small_linear(const float* x, int M, int K, const float* W, const float* b, int N, int silu_in,
+                                   int silu_out, float* y, void* stream) {
+  B200AD_REQUIRE(M >= 1 && M <= 8, "small_linear: M=%d (1..8)", M);
+  B200AD_REQUIRE(K % 4 == 0, "small_linear: K=%d must be a multiple of 4", K);
+  const int threads = 256;
+  const int blocks = (int)(((long long)N * 32 + threads - 1) / threads);
+  small_linear_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(x, M, K, W, b, N, silu_in, silu_out, y);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200ad_conv_in(const float* sample, int B, int cin, int F, int h, int w, const float* W,
+                              const float* bias, int cout, float* out_nhwc, void* stream) {
+  B200AD_REQUIRE(cin * 9 <= CIN_MAXK, "conv_in: cin=%d too large for the direct kernel", cin);
+  const long long npix = (long long)B * F * h * w;
+  const int threads = cout >= 320 ? 320 : ((cout + 31) / 32 * 32);
+  conv_in_kernel<<<(unsigned)((npix + CIN_PIX - 1) / CIN_PIX), threads, 0, (cudaStream_t)stream>>>(
+      sample, B, cin, F, h, w, W, bias, cout, out_nhwc);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200ad_conv_out(int op_dtype, const void* act_nhwc, int B, int F, int h, int w, int cin,
+                               const float* W, const float* bias, int cout, float* out_bcfhw, void* stream) {
+  B200AD_REQUIRE(cout >= 1 && cout <= 4 && cin % 2 == 0, "conv_out: cin=%d cout=%d unsupported", cin, cout);
+  const size_t smem = (size_t)cout * 9 * cin * sizeof(float);
+  B200AD_REQUIRE(smem <= 96 * 1024, "conv_out: weights need %zu bytes of shared memory", smem);
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(conv_out_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(conv_out_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    attr_set = true;
+  }
+  const long long npix = (long long)B * F * h * w;
+  const int threads = 512;     // 16 pixels per block amortise the weight staging
+  const long long blocks = (npix * 32 + threads - 1) / threads;
+  if (op_dtype == 0)
+    conv_out_kernel<bf16><<<(unsigned)blocks, threads, smem, (cudaStream_t)stream>>>((const bf16*)act_nhwc, B, F, h, w, cin, W, bias, cout, out_bcfhw);
+  else
+    conv_out_kernel<float><<<(unsigned)blocks, threads, smem, (cudaStream_t)stream>>>((const float*)act_nhwc, B, F, h, w, cin, W, bias, cout, out_bcfhw);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200ad_cfg_step(const float* eps_u, const float* eps_c, const float* latents, float g, float cx,
+                               float ce, float in_scale, long long n, float* latents_out, float* model_in,
+                               int model_in_copies, void* stream) {
+  B200AD_REQUIRE(n % 4 == 0, "cfg_step: n=%lld must be a multiple of 4", n);
+  const long long n4 = n / 4;
+  const int threads = 256;
+  cfg_step_kernel<<<(unsigned)((n4 + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
+      (const float4*)eps_u, (const float4*)eps_c, (const float4*)latents, g, cx, ce, in_scale, n4,
+      (float4*)latents_out, (float4*)model_in, model_in_copies);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

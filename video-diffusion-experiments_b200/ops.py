@@ -1,0 +1,206 @@
+"""Functional wrappers over the C ABI: torch tensors in, torch tensors out.
+
+PyTorch is plumbing here (device memory, the current stream); every computation is a kernel in libb200ad.so.
+All functions require CUDA tensors and raise otherwise -- there is no CPU fallback.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import lib as _lib
+
+BF16, FP32 = 0, 1
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.B200ADError("b200ad kernels need CUDA tensors (no CPU fallback exists)")
+
+
+class Ops:
+    """Kernel front-end bound to one operand mode: 'bf16' (tcgen05 tensor cores) or 'fp32' (SIMT)."""
+
+    def __init__(self, mode: str = "bf16"):
+        if mode not in ("bf16", "fp32"):
+            raise ValueError(f"mode must be 'bf16' or 'fp32', got {mode!r}")
+        self.mode = mode
+        self.op = BF16 if mode == "bf16" else FP32
+        self.op_dtype = torch.bfloat16 if mode == "bf16" else torch.float32
+        self.L = _lib.load()
+
+    # ---------------------------------------------------------------- contractions
+    def gemm(self, a, w, *, bias=None, row_bias=None, rb_div=1, residual=None, out_f32=None, out_op=None,
+             want_f32=False, want_op=False, geglu=False):
+        """C = a[M,K] @ w[N,K]^T with fused epilogue (b200ad_gemm).  Returns (out_f32, out_op)."""
+        _need_cuda(a, w)
+        assert a.dim() == 2 and w.dim() == 2 and a.dtype == self.op_dtype and w.dtype == self.op_dtype
+        assert a.stride(1) == 1 and w.is_contiguous()
+        M, K = a.shape
+        N = w.shape[0]
+        assert w.shape[1] == K
+        n_out = N // 2 if geglu else N
+        if want_f32 and out_f32 is None:
+            out_f32 = torch.empty((M, n_out), device=a.device, dtype=torch.float32)
+        if want_op and out_op is None:
+            out_op = torch.empty((M, n_out), device=a.device, dtype=self.op_dtype)
+        rc = self.L.b200ad_gemm(
+            self.op, a.data_ptr(), a.stride(0), w.data_ptr(), M, N, K, _ptr(bias), _ptr(row_bias), rb_div,
+            0 if row_bias is None else row_bias.stride(0), _ptr(residual),
+            0 if residual is None else residual.stride(0), _ptr(out_f32),
+            0 if out_f32 is None else out_f32.stride(0), _ptr(out_op), 0 if out_op is None else out_op.stride(0),
+            1 if geglu else 0, _stream())
+        _lib.check(rc, "b200ad_gemm")
+        return out_f32, out_op
+
+    def conv3x3(self, src, w, nimg, h, wd, *, stride2=False, bias=None, row_bias=None, rb_div=1, residual=None,
+                want_f32=True, want_op=False):
+        """3x3 conv over NHWC `src` (operand-typed); w [cout, 9*cin].  Returns (out_f32 [nimg*h*wd, cout], out_op)."""
+        _need_cuda(src, w)
+        assert src.dtype == self.op_dtype and w.dtype == self.op_dtype and src.is_contiguous() and w.is_contiguous()
+        cout, k9 = w.shape
+        cin = k9 // 9
+        M = nimg * h * wd
+        out_f32 = torch.empty((M, cout), device=src.device, dtype=torch.float32) if want_f32 else None
+        out_op = torch.empty((M, cout), device=src.device, dtype=self.op_dtype) if want_op else None
+        rc = self.L.b200ad_conv3x3(
+            self.op, src.data_ptr(), w.data_ptr(), nimg, h, wd, cin, cout, 1 if stride2 else 0, _ptr(bias),
+            _ptr(row_bias), rb_div, 0 if row_bias is None else row_bias.stride(0), _ptr(residual),
+            0 if residual is None else residual.stride(0), _ptr(out_f32), cout, _ptr(out_op), cout, _stream())
+        _lib.check(rc, "b200ad_conv3x3")
+        return out_f32, out_op
+
+    def attention(self, q, k, v, nbatch, heads, Lq, Lk, d, dpad, kv_div=1):
+        """q/k/v: 2-D operand-typed views (row stride = leading dim).  Returns [nbatch*Lq, heads*d]."""
+        _need_cuda(q, k, v)
+        out = torch.empty((nbatch * Lq, heads * d), device=q.device, dtype=self.op_dtype)
+        rc = self.L.b200ad_attention(self.op, q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(),
+                                     v.stride(0), nbatch, heads, Lq, Lk, d, dpad, kv_div, out.data_ptr(),
+                                     out.stride(0), _stream())
+        _lib.check(rc, "b200ad_attention")
+        return out
+
+    def temporal_attention(self, qkv, B, F, hw, C, heads):
+        _need_cuda(qkv)
+        assert qkv.is_contiguous() and qkv.shape == (B * F * hw, 3 * C)
+        out = torch.empty((B * F * hw, C), device=qkv.device, dtype=self.op_dtype)
+        rc = self.L.b200ad_temporal_attention(self.op, qkv.data_ptr(), B, F, hw, C, heads, out.data_ptr(), _stream())
+        _lib.check(rc, "b200ad_temporal_attention")
+        return out
+
+    # ---------------------------------------------------------------- norms / re-layout
+    def group_norm(self, x0, x1, nimg, hw, groups, gamma, beta, eps, *, silu, frames_per_stat=1, want_raw=False):
+        """GroupNorm(+SiLU) of cat([x0, x1], channel) for fp32 [nimg*hw, c] inputs -> operand-typed output."""
+        _need_cuda(x0, x1)
+        assert x0.dtype == torch.float32 and x0.is_contiguous()
+        c0 = x0.shape[-1]
+        c1 = 0 if x1 is None else x1.shape[-1]
+        if x1 is not None:
+            assert x1.dtype == torch.float32 and x1.is_contiguous()
+        nblk = self.L.b200ad_gn_nblk(hw)
+        partial = torch.empty((nimg * nblk * groups + nimg * groups, 2), device=x0.device, dtype=torch.float32)
+        rc = self.L.b200ad_gn_stats(x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups, partial.data_ptr(), _stream())
+        _lib.check(rc, "b200ad_gn_stats")
+        out = torch.empty((nimg * hw, c0 + c1), device=x0.device, dtype=self.op_dtype)
+        raw = torch.empty_like(out) if want_raw else None
+        rc = self.L.b200ad_gn_apply(self.op, x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups, partial.data_ptr(),
+                                    frames_per_stat, float(eps), gamma.data_ptr(), beta.data_ptr(),
+                                    1 if silu else 0, out.data_ptr(), _ptr(raw), _stream())
+        _lib.check(rc, "b200ad_gn_apply")
+        return (out, raw) if want_raw else out
+
+    def layer_norm(self, x, gamma, beta, eps=1e-5, pe=None, hw=1, frames=1):
+        _need_cuda(x)
+        assert x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2
+        rows, C = x.shape
+        out = torch.empty((rows, C), device=x.device, dtype=self.op_dtype)
+        rc = self.L.b200ad_layernorm(self.op, x.data_ptr(), rows, C, gamma.data_ptr(), beta.data_ptr(), float(eps),
+                                     _ptr(pe), hw, frames, out.data_ptr(), _stream())
+        _lib.check(rc, "b200ad_layernorm")
+        return out
+
+    def cast(self, x, nimg, h, w, C, mode=0):
+        """fp32 NHWC -> operand type; mode 0 plain, 1 space-to-depth phase split, 2 nearest x2 upsample."""
+        _need_cuda(x)
+        assert x.dtype == torch.float32 and x.is_contiguous()
+        if mode == 0:
+            shape = (nimg * h * w, C)
+        elif mode == 1:
+            shape = (4 * nimg * (h // 2) * (w // 2), C)
+        else:
+            shape = (nimg * 4 * h * w, C)
+        out = torch.empty(shape, device=x.device, dtype=self.op_dtype)
+        rc = self.L.b200ad_cast(self.op, x.data_ptr(), nimg, h, w, C, mode, out.data_ptr(), _stream())
+        _lib.check(rc, "b200ad_cast")
+        return out
+
+    # ---------------------------------------------------------------- small ops
+    def timestep_sinusoid(self, t, dim):
+        _need_cuda(t)
+        assert t.dtype == torch.float32 and t.dim() == 1
+        out = torch.empty((t.shape[0], dim), device=t.device, dtype=torch.float32)
+        _lib.check(self.L.b200ad_timestep_sinusoid(t.data_ptr(), t.shape[0], dim, out.data_ptr(), _stream()),
+                   "b200ad_timestep_sinusoid")
+        return out
+
+    def small_linear(self, x, w, b, silu_in=False, silu_out=False):
+        _need_cuda(x, w)
+        assert x.dtype == torch.float32 and w.dtype == torch.float32 and x.is_contiguous() and w.is_contiguous()
+        M, K = x.shape
+        N = w.shape[0]
+        y = torch.empty((M, N), device=x.device, dtype=torch.float32)
+        _lib.check(self.L.b200ad_small_linear(x.data_ptr(), M, K, w.data_ptr(), _ptr(b), N, int(silu_in),
+                                              int(silu_out), y.data_ptr(), _stream()), "b200ad_small_linear")
+        return y
+
+    def conv_in(self, sample, w, b):
+        _need_cuda(sample, w)
+        assert sample.dtype == torch.float32 and sample.is_contiguous() and sample.dim() == 5
+        B, cin, F, h, wd = sample.shape
+        cout = w.shape[0]
+        out = torch.empty((B * F * h * wd, cout), device=sample.device, dtype=torch.float32)
+        _lib.check(self.L.b200ad_conv_in(sample.data_ptr(), B, cin, F, h, wd, w.data_ptr(), _ptr(b), cout,
+                                         out.data_ptr(), _stream()), "b200ad_conv_in")
+        return out
+
+    def conv_out(self, act, B, F, h, wd, w, b):
+        _need_cuda(act, w)
+        cout, cin = w.shape[0], w.shape[1]
+        assert act.dtype == self.op_dtype and act.is_contiguous()
+        out = torch.empty((B, cout, F, h, wd), device=act.device, dtype=torch.float32)
+        _lib.check(self.L.b200ad_conv_out(self.op, act.data_ptr(), B, F, h, wd, cin, w.data_ptr(), _ptr(b), cout,
+                                          out.data_ptr(), _stream()), "b200ad_conv_out")
+        return out
+
+    def cfg_step(self, eps_u, eps_c, latents, g, cx, ce, in_scale=1.0, latents_out=None, model_in=None):
+        """latents' = cx*latents + ce*(eps_u + g*(eps_c-eps_u)); model_in[k] = latents'*in_scale."""
+        _need_cuda(eps_u, eps_c, latents)
+        for t in (eps_u, eps_c, latents):
+            assert t.dtype == torch.float32 and t.is_contiguous()
+        n = latents.numel()
+        if latents_out is None:
+            latents_out = torch.empty_like(latents)
+        copies = 0 if model_in is None else model_in.numel() // n
+        _lib.check(self.L.b200ad_cfg_step(eps_u.data_ptr(), eps_c.data_ptr(), latents.data_ptr(), float(g),
+                                          float(cx), float(ce), float(in_scale), n, latents_out.data_ptr(),
+                                          _ptr(model_in), copies, _stream()), "b200ad_cfg_step")
+        return latents_out
+
+
+_OPS = {}
+
+
+def get_ops(mode: str = "bf16") -> Ops:
+    if mode not in _OPS:
+        _OPS[mode] = Ops(mode)
+    return _OPS[mode]
