@@ -111,6 +111,10 @@ int b200ad_conv_out(int op_dtype, const void* act_nhwc, int B, int F, int h, int
 int b200ad_cfg_step(const float* eps_u, const float* eps_c, const float* latents, float g, float cx, float ce,
                     float in_scale, long long n, float* latents_out, float* model_in, int model_in_copies,
                     void* stream);
+/* Same update with (g, cx, ce, in_scale) read from 16-byte-aligned DEVICE memory: a CUDA graph captured once
+ * is replayed for every denoise step after a 16-byte parameter upload (no per-step re-capture, no host sync). */
+int b200ad_cfg_step_dev(const float* eps_u, const float* eps_c, const float* latents, const float* dev_coef4,
+                        long long n, float* latents_out, float* model_in, int model_in_copies, void* stream);
 
 #ifdef __cplusplus
 }

@@ -140,12 +140,17 @@ __global__ void conv_out_kernel(const T* __restrict__ act, int B, int F, int h, 
 }
 
 // guided = u + g*(c-u); x' = cx*x + ce*guided; model_in[k] = x'*in_scale for k < copies
+// dev_coef (optional): [g, cx, ce, in_scale] in device memory, so that one captured CUDA graph serves every step.
 __global__ void cfg_step_kernel(const float4* __restrict__ eu, const float4* __restrict__ ec,
                                 const float4* __restrict__ lat, float g, float cx, float ce, float in_scale,
-                                long long n4, float4* __restrict__ lat_out, float4* __restrict__ model_in,
-                                int copies) {
+                                const float* __restrict__ dev_coef, long long n4, float4* __restrict__ lat_out,
+                                float4* __restrict__ model_in, int copies) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n4) return;
+  if (dev_coef) {
+    const float4 k = *reinterpret_cast<const float4*>(dev_coef);
+    g = k.x; cx = k.y; ce = k.z; in_scale = k.w;
+  }
   const float4 u = eu[i], c = ec[i], x = lat[i];
   float4 r;
   r.x = cx * x.x + ce * (u.x + g * (c.x - u.x));
@@ -226,7 +231,22 @@ extern "C" int b200ad_cfg_step(const float* eps_u, const float* eps_c, const flo
   const long long n4 = n / 4;
   const int threads = 256;
   cfg_step_kernel<<<(unsigned)((n4 + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
-      (const float4*)eps_u, (const float4*)eps_c, (const float4*)latents, g, cx, ce, in_scale, n4,
+      (const float4*)eps_u, (const float4*)eps_c, (const float4*)latents, g, cx, ce, in_scale, nullptr, n4,
+      (float4*)latents_out, (float4*)model_in, model_in_copies);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200ad_cfg_step_dev(const float* eps_u, const float* eps_c, const float* latents,
+                                   const float* dev_coef4, long long n, float* latents_out, float* model_in,
+                                   int model_in_copies, void* stream) {
+  B200AD_REQUIRE(n % 4 == 0, "cfg_step_dev: n=%lld must be a multiple of 4", n);
+  B200AD_REQUIRE(dev_coef4 && ((uintptr_t)dev_coef4 & 15) == 0, "cfg_step_dev: coefficient pointer must be 16-byte aligned");
+  const long long n4 = n / 4;
+  const int threads = 256;
+  cfg_step_kernel<<<(unsigned)((n4 + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
+      (const float4*)eps_u, (const float4*)eps_c, (const float4*)latents, 0.f, 0.f, 0.f, 0.f, dev_coef4, n4,
       (float4*)latents_out, (float4*)model_in, model_in_copies);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());

@@ -36,6 +36,7 @@ SIGNATURES = {
     "b200ad_conv_in": [_P, _I, _I, _I, _I, _I, _P, _P, _I, _P, _P],
     "b200ad_conv_out": [_I, _P, _I, _I, _I, _I, _I, _P, _P, _I, _P, _P],
     "b200ad_cfg_step": [_P, _P, _P, _F, _F, _F, _F, _L, _P, _P, _I, _P],
+    "b200ad_cfg_step_dev": [_P, _P, _P, _P, _L, _P, _P, _I, _P],
 }
 _RESTYPES = {"b200ad_last_error": c_char_p, "b200ad_launch_count": c_longlong}
 

@@ -28,8 +28,58 @@ def _need_cuda(*ts):
             raise _lib.B200ADError("b200ad kernels need CUDA tensors (no CPU fallback exists)")
 
 
+class KernelProfiler:
+    """Per-kernel-family timing with CUDA events on the launching stream (eager launches only; bench.py uses it
+    for the roofline numbers).  Each record: family, algorithmic FLOPs, algorithmic bytes, (start, end) events."""
+
+    def __init__(self):
+        self.records = []
+
+    def summary(self):
+        torch.cuda.synchronize()
+        fam = {}
+        for name, flops, nbytes, e0, e1 in self.records:
+            d = fam.setdefault(name, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+            d["launches"] += 1
+            d["ms"] += e0.elapsed_time(e1)
+            d["flops"] += flops
+            d["bytes"] += nbytes
+        for d in fam.values():
+            sec = max(d["ms"], 1e-9) * 1e-3
+            d["tflops"] = d["flops"] / sec / 1e12
+            d["gbs"] = d["bytes"] / sec / 1e9
+        return fam
+
+
+class _Rec:
+    __slots__ = ("prof", "name", "flops", "nbytes", "e0")
+
+    def __init__(self, prof, name, flops, nbytes):
+        self.prof, self.name, self.flops, self.nbytes = prof, name, flops, nbytes
+
+    def __enter__(self):
+        if self.prof is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *exc):
+        if self.prof is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            self.prof.records.append((self.name, self.flops, self.nbytes, self.e0, e1))
+        return False
+
+
+def _nb(*ts):
+    return float(sum(t.numel() * t.element_size() for t in ts if t is not None))
+
+
 class Ops:
     """Kernel front-end bound to one operand mode: 'bf16' (tcgen05 tensor cores) or 'fp32' (SIMT)."""
+    profiler: Optional[KernelProfiler] = None       # class-level: set by bench.py around an eager pass
+
+    def _rec(self, name, flops=0.0, nbytes=0.0):
+        return _Rec(Ops.profiler, name, flops, nbytes)
 
     def __init__(self, mode: str = "bf16"):
         if mode not in ("bf16", "fp32"):
@@ -54,12 +104,13 @@ class Ops:
             out_f32 = torch.empty((M, n_out), device=a.device, dtype=torch.float32)
         if want_op and out_op is None:
             out_op = torch.empty((M, n_out), device=a.device, dtype=self.op_dtype)
-        rc = self.L.b200ad_gemm(
-            self.op, a.data_ptr(), a.stride(0), w.data_ptr(), M, N, K, _ptr(bias), _ptr(row_bias), rb_div,
-            0 if row_bias is None else row_bias.stride(0), _ptr(residual),
-            0 if residual is None else residual.stride(0), _ptr(out_f32),
-            0 if out_f32 is None else out_f32.stride(0), _ptr(out_op), 0 if out_op is None else out_op.stride(0),
-            1 if geglu else 0, _stream())
+        with self._rec("gemm", 2.0 * M * N * K, _nb(w, residual, out_f32, out_op) + M * K * a.element_size()):
+            rc = self.L.b200ad_gemm(
+                self.op, a.data_ptr(), a.stride(0), w.data_ptr(), M, N, K, _ptr(bias), _ptr(row_bias), rb_div,
+                0 if row_bias is None else row_bias.stride(0), _ptr(residual),
+                0 if residual is None else residual.stride(0), _ptr(out_f32),
+                0 if out_f32 is None else out_f32.stride(0), _ptr(out_op),
+                0 if out_op is None else out_op.stride(0), 1 if geglu else 0, _stream())
         _lib.check(rc, "b200ad_gemm")
         return out_f32, out_op
 
@@ -73,10 +124,11 @@ class Ops:
         M = nimg * h * wd
         out_f32 = torch.empty((M, cout), device=src.device, dtype=torch.float32) if want_f32 else None
         out_op = torch.empty((M, cout), device=src.device, dtype=self.op_dtype) if want_op else None
-        rc = self.L.b200ad_conv3x3(
-            self.op, src.data_ptr(), w.data_ptr(), nimg, h, wd, cin, cout, 1 if stride2 else 0, _ptr(bias),
-            _ptr(row_bias), rb_div, 0 if row_bias is None else row_bias.stride(0), _ptr(residual),
-            0 if residual is None else residual.stride(0), _ptr(out_f32), cout, _ptr(out_op), cout, _stream())
+        with self._rec("conv3x3", 2.0 * M * cout * k9, _nb(src, w, residual, out_f32, out_op)):
+            rc = self.L.b200ad_conv3x3(
+                self.op, src.data_ptr(), w.data_ptr(), nimg, h, wd, cin, cout, 1 if stride2 else 0, _ptr(bias),
+                _ptr(row_bias), rb_div, 0 if row_bias is None else row_bias.stride(0), _ptr(residual),
+                0 if residual is None else residual.stride(0), _ptr(out_f32), cout, _ptr(out_op), cout, _stream())
         _lib.check(rc, "b200ad_conv3x3")
         return out_f32, out_op
 
@@ -84,9 +136,12 @@ class Ops:
         """q/k/v: 2-D operand-typed views (row stride = leading dim).  Returns [nbatch*Lq, heads*d]."""
         _need_cuda(q, k, v)
         out = torch.empty((nbatch * Lq, heads * d), device=q.device, dtype=self.op_dtype)
-        rc = self.L.b200ad_attention(self.op, q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(),
-                                     v.stride(0), nbatch, heads, Lq, Lk, d, dpad, kv_div, out.data_ptr(),
-                                     out.stride(0), _stream())
+        es = out.element_size()
+        nbytes = es * heads * d * (2.0 * nbatch * Lq + 2.0 * (nbatch // kv_div) * Lk)
+        with self._rec("attention_L%d_d%d" % (Lk, d), 4.0 * nbatch * heads * Lq * Lk * d, nbytes):
+            rc = self.L.b200ad_attention(self.op, q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(),
+                                         v.stride(0), nbatch, heads, Lq, Lk, d, dpad, kv_div, out.data_ptr(),
+                                         out.stride(0), _stream())
         _lib.check(rc, "b200ad_attention")
         return out
 
@@ -94,7 +149,9 @@ class Ops:
         _need_cuda(qkv)
         assert qkv.is_contiguous() and qkv.shape == (B * F * hw, 3 * C)
         out = torch.empty((B * F * hw, C), device=qkv.device, dtype=self.op_dtype)
-        rc = self.L.b200ad_temporal_attention(self.op, qkv.data_ptr(), B, F, hw, C, heads, out.data_ptr(), _stream())
+        with self._rec("temporal_attention", 4.0 * B * hw * F * F * C, _nb(qkv, out)):
+            rc = self.L.b200ad_temporal_attention(self.op, qkv.data_ptr(), B, F, hw, C, heads, out.data_ptr(),
+                                                  _stream())
         _lib.check(rc, "b200ad_temporal_attention")
         return out
 
@@ -109,13 +166,16 @@ class Ops:
             assert x1.dtype == torch.float32 and x1.is_contiguous()
         nblk = self.L.b200ad_gn_nblk(hw)
         partial = torch.empty((nimg * nblk * groups + nimg * groups, 2), device=x0.device, dtype=torch.float32)
-        rc = self.L.b200ad_gn_stats(x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups, partial.data_ptr(), _stream())
+        with self._rec("gn_stats", 0.0, _nb(x0, x1)):
+            rc = self.L.b200ad_gn_stats(x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups, partial.data_ptr(),
+                                        _stream())
         _lib.check(rc, "b200ad_gn_stats")
         out = torch.empty((nimg * hw, c0 + c1), device=x0.device, dtype=self.op_dtype)
         raw = torch.empty_like(out) if want_raw else None
-        rc = self.L.b200ad_gn_apply(self.op, x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups, partial.data_ptr(),
-                                    frames_per_stat, float(eps), gamma.data_ptr(), beta.data_ptr(),
-                                    1 if silu else 0, out.data_ptr(), _ptr(raw), _stream())
+        with self._rec("gn_apply", 0.0, _nb(x0, x1, out, raw)):
+            rc = self.L.b200ad_gn_apply(self.op, x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups,
+                                        partial.data_ptr(), frames_per_stat, float(eps), gamma.data_ptr(),
+                                        beta.data_ptr(), 1 if silu else 0, out.data_ptr(), _ptr(raw), _stream())
         _lib.check(rc, "b200ad_gn_apply")
         return (out, raw) if want_raw else out
 
@@ -124,8 +184,9 @@ class Ops:
         assert x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2
         rows, C = x.shape
         out = torch.empty((rows, C), device=x.device, dtype=self.op_dtype)
-        rc = self.L.b200ad_layernorm(self.op, x.data_ptr(), rows, C, gamma.data_ptr(), beta.data_ptr(), float(eps),
-                                     _ptr(pe), hw, frames, out.data_ptr(), _stream())
+        with self._rec("layernorm", 0.0, _nb(x, out)):
+            rc = self.L.b200ad_layernorm(self.op, x.data_ptr(), rows, C, gamma.data_ptr(), beta.data_ptr(),
+                                         float(eps), _ptr(pe), hw, frames, out.data_ptr(), _stream())
         _lib.check(rc, "b200ad_layernorm")
         return out
 
@@ -140,7 +201,8 @@ class Ops:
         else:
             shape = (nimg * 4 * h * w, C)
         out = torch.empty(shape, device=x.device, dtype=self.op_dtype)
-        rc = self.L.b200ad_cast(self.op, x.data_ptr(), nimg, h, w, C, mode, out.data_ptr(), _stream())
+        with self._rec("cast", 0.0, _nb(out) * (1.0 + 4.0 / out.element_size() / (4 if mode == 2 else 1))):
+            rc = self.L.b200ad_cast(self.op, x.data_ptr(), nimg, h, w, C, mode, out.data_ptr(), _stream())
         _lib.check(rc, "b200ad_cast")
         return out
 
@@ -159,8 +221,9 @@ class Ops:
         M, K = x.shape
         N = w.shape[0]
         y = torch.empty((M, N), device=x.device, dtype=torch.float32)
-        _lib.check(self.L.b200ad_small_linear(x.data_ptr(), M, K, w.data_ptr(), _ptr(b), N, int(silu_in),
-                                              int(silu_out), y.data_ptr(), _stream()), "b200ad_small_linear")
+        with self._rec("small_linear", 2.0 * M * N * K, _nb(w, x, y)):
+            _lib.check(self.L.b200ad_small_linear(x.data_ptr(), M, K, w.data_ptr(), _ptr(b), N, int(silu_in),
+                                                  int(silu_out), y.data_ptr(), _stream()), "b200ad_small_linear")
         return y
 
     def conv_in(self, sample, w, b):
@@ -169,8 +232,9 @@ class Ops:
         B, cin, F, h, wd = sample.shape
         cout = w.shape[0]
         out = torch.empty((B * F * h * wd, cout), device=sample.device, dtype=torch.float32)
-        _lib.check(self.L.b200ad_conv_in(sample.data_ptr(), B, cin, F, h, wd, w.data_ptr(), _ptr(b), cout,
-                                         out.data_ptr(), _stream()), "b200ad_conv_in")
+        with self._rec("conv_in", 2.0 * B * F * h * wd * cout * cin * 9, _nb(sample, out)):
+            _lib.check(self.L.b200ad_conv_in(sample.data_ptr(), B, cin, F, h, wd, w.data_ptr(), _ptr(b), cout,
+                                             out.data_ptr(), _stream()), "b200ad_conv_in")
         return out
 
     def conv_out(self, act, B, F, h, wd, w, b):
@@ -178,8 +242,9 @@ class Ops:
         cout, cin = w.shape[0], w.shape[1]
         assert act.dtype == self.op_dtype and act.is_contiguous()
         out = torch.empty((B, cout, F, h, wd), device=act.device, dtype=torch.float32)
-        _lib.check(self.L.b200ad_conv_out(self.op, act.data_ptr(), B, F, h, wd, cin, w.data_ptr(), _ptr(b), cout,
-                                          out.data_ptr(), _stream()), "b200ad_conv_out")
+        with self._rec("conv_out", 2.0 * B * F * h * wd * cout * cin * 9, _nb(act, out)):
+            _lib.check(self.L.b200ad_conv_out(self.op, act.data_ptr(), B, F, h, wd, cin, w.data_ptr(), _ptr(b), cout,
+                                              out.data_ptr(), _stream()), "b200ad_conv_out")
         return out
 
     def cfg_step(self, eps_u, eps_c, latents, g, cx, ce, in_scale=1.0, latents_out=None, model_in=None):
@@ -194,6 +259,18 @@ class Ops:
         _lib.check(self.L.b200ad_cfg_step(eps_u.data_ptr(), eps_c.data_ptr(), latents.data_ptr(), float(g),
                                           float(cx), float(ce), float(in_scale), n, latents_out.data_ptr(),
                                           _ptr(model_in), copies, _stream()), "b200ad_cfg_step")
+        return latents_out
+
+
+    def cfg_step_dev(self, eps_u, eps_c, latents, coef4, latents_out, model_in=None):
+        """cfg_step with (g, cx, ce, in_scale) in device memory `coef4` (graph-replayable)."""
+        _need_cuda(eps_u, eps_c, latents, coef4)
+        n = latents.numel()
+        copies = 0 if model_in is None else model_in.numel() // n
+        with self._rec("cfg_step", 0.0, 4.0 * n * (4 + copies)):
+            _lib.check(self.L.b200ad_cfg_step_dev(eps_u.data_ptr(), eps_c.data_ptr(), latents.data_ptr(),
+                                                  coef4.data_ptr(), n, latents_out.data_ptr(), _ptr(model_in),
+                                                  copies, _stream()), "b200ad_cfg_step_dev")
         return latents_out
 
 

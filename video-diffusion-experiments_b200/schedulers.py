@@ -68,6 +68,10 @@ class _SchedulerBase:
         """(c_x, c_eps, next_in_scale) of step i: x' = c_x*x + c_eps*eps; next model input = x'*next_in_scale."""
         return self._cx[i], self._ce[i], self._next_scale[i]
 
+    def first_in_scale(self) -> float:
+        """scale_model_input factor of the first step (1 for DDIM)."""
+        return 1.0
+
     def _step_index_of(self, timestep) -> int:
         t = float(timestep)
         ts = self._timesteps_host
@@ -213,3 +217,17 @@ SD15_SCHEDULER_CONFIG = FrozenConfig(
     _class_name="PNDMScheduler", num_train_timesteps=1000, beta_start=0.00085, beta_end=0.012,
     beta_schedule="scaled_linear", trained_betas=None, skip_prk_steps=True, set_alpha_to_one=False,
     prediction_type="epsilon", timestep_spacing="leading", steps_offset=1, clip_sample=False)
+
+
+class PNDMPlaceholder:
+    """What ``from_pretrained`` leaves in ``pipe.scheduler``: SD1.5 ships a PNDM config, and every reference
+    script replaces it via ``XScheduler.from_config(pipe.scheduler.config, ...)`` before generating
+    (05_grid_search_ablation.py:136-141, 01_baseline_generation.py:76-80).  Only ``.config`` is usable."""
+
+    def __init__(self, config):
+        self.config = config
+
+    def __getattr__(self, k):
+        raise NotImplementedError(
+            f"PNDMScheduler.{k}: PNDM is not implemented; assign DDIMScheduler.from_config(pipe.scheduler.config, ...)"
+            " or EulerDiscreteScheduler.from_config(...) as the reference scripts do")

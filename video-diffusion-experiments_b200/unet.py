@@ -85,12 +85,13 @@ def _pad_heads(w: torch.Tensor, heads: int, dpad: int) -> torch.Tensor:
 
 class _State:
     """Per-forward context handed down the tree."""
-    __slots__ = ("o", "B", "F", "temb", "ctx", "kv_div", "kv_cache")
+    __slots__ = ("o", "B", "F", "temb", "ctx", "ctx_rows", "kv_div", "kv_cache")
 
     def __init__(self, o: Ops, B: int, F: int):
         self.o, self.B, self.F = o, B, F
         self.temb = None        # [B, sum(cout)] fp32: all time_emb_proj outputs of the step (one launch)
         self.ctx = None         # operand-typed text rows [Bt*77, 768]
+        self.ctx_rows = 0
         self.kv_div = 1         # frames sharing one text row
         self.kv_cache = None    # dict: id(module) -> (kv buffer) for cross-attention K/V of the text
 
@@ -179,7 +180,7 @@ class Attention(_Packable):
             if st.kv_cache is not None:
                 st.kv_cache[id(self)] = kv
         _, q = o.gemm(n_op, p["wq"], want_op=True)
-        Lk = st.ctx.shape[0] // (nimg // st.kv_div)
+        Lk = st.ctx_rows // (nimg // st.kv_div)
         att = o.attention(q, kv[:, :hd], kv[:, hd:], nimg, H, L, Lk, C // H, dp, st.kv_div)
         o.gemm(att, p["wo"], bias=p["bo"], residual=h, out_f32=h)
         return h
@@ -737,7 +738,23 @@ class UNetMotionModel(_Packable):
         self._kv_cache_key = None
 
     @torch.no_grad()
-    def forward(self, sample, timestep, encoder_hidden_states, **kw):
+    def text_kv(self, encoder_hidden_states, out: Optional[dict] = None) -> dict:
+        """Cross-attention K|V projections of the text for all 16 spatial transformers (they depend on neither
+        the timestep nor the latents: once per video).  With `out` (a previous result) the buffers are
+        overwritten in place, so a captured CUDA graph that reads them sees the new prompt."""
+        o = get_ops(self.mode)
+        e2 = encoder_hidden_states.reshape(-1, encoder_hidden_states.shape[-1]).float().contiguous()
+        ctx = o.cast(e2, 1, 1, e2.shape[0], e2.shape[1], mode=0)
+        res = out if out is not None else {}
+        for m in self.modules():
+            if isinstance(m, Attention) and m.is_cross_attention:
+                p = m.packed_cross(o)
+                res[id(m)] = o.gemm(ctx, p["wkv"], out_op=res.get(id(m)), want_op=True)[1]
+        res["rows"] = e2.shape[0]
+        return res
+
+    @torch.no_grad()
+    def forward(self, sample, timestep, encoder_hidden_states, text_kv=None, **kw):
         if not sample.is_cuda:
             raise RuntimeError("UNetMotionModel: CUDA tensors required (the b200ad path has no CPU fallback)")
         o = get_ops(self.mode)
@@ -755,13 +772,19 @@ class UNetMotionModel(_Packable):
             st.kv_div = 1
         else:
             raise ValueError(f"encoder_hidden_states batch {ehs.shape[0]} is neither B={B} nor B*F={nimg}")
-        if self._kv_cache is not None:
-            key = (ehs.data_ptr(), ehs._version, tuple(ehs.shape), self.mode)
-            if key != self._kv_cache_key:
-                self._kv_cache, self._kv_cache_key = {}, key
-            st.kv_cache = self._kv_cache
-        e2 = ehs.reshape(-1, ehs.shape[-1]).float().contiguous()
-        st.ctx = o.cast(e2, 1, 1, e2.shape[0], e2.shape[1], mode=0)
+        if text_kv is not None:                       # caller-owned K/V buffers (DenoisePlan / CUDA graph)
+            st.kv_cache, st.ctx_rows = text_kv, text_kv["rows"]
+            if st.ctx_rows != ehs.shape[0] * ehs.shape[1]:
+                raise ValueError("text_kv was computed for a different encoder_hidden_states shape")
+        else:
+            if self._kv_cache is not None:
+                key = (ehs.data_ptr(), ehs._version, tuple(ehs.shape), self.mode)
+                if key != self._kv_cache_key:
+                    self._kv_cache, self._kv_cache_key = {}, key
+                st.kv_cache = self._kv_cache
+            e2 = ehs.reshape(-1, ehs.shape[-1]).float().contiguous()
+            st.ctx = o.cast(e2, 1, 1, e2.shape[0], e2.shape[1], mode=0)
+            st.ctx_rows = e2.shape[0]
         # time embedding: sinusoid -> Linear -> SiLU -> Linear, then every resnet's Linear(SiLU(emb)) in one launch
         t = self._timestep_tensor(timestep, B)
         emb = o.timestep_sinusoid(t, self.cfg.block_out_channels[0])
