@@ -1,0 +1,159 @@
+"""CPU tests (-m "not gpu") of the host side: scheduler tables of the product against the oracle and the golden
+fixtures, the C-ABI library (loads, exports every symbol of include/b200ad.h, fails loudly without a GPU), and the
+diffusers-compatible import surface the reference uses (05_grid_search_ablation.py:27-28)."""
+import ctypes
+import json
+import os
+import re
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+import b200ad  # noqa: E402,F401
+from b200ad import lib  # noqa: E402
+from b200ad.schedulers import SD15_SCHEDULER_CONFIG, DDIMScheduler, EulerDiscreteScheduler  # noqa: E402
+
+
+def _ddim():
+    return DDIMScheduler.from_config(SD15_SCHEDULER_CONFIG, beta_schedule="linear", steps_offset=1, clip_sample=False)
+
+
+@pytest.fixture(scope="module")
+def golden():
+    with open(os.path.join(GOLDEN, "schedulers.json")) as f:
+        return json.load(f)
+
+
+@pytest.mark.parametrize("n", [15, 20, 25, 30, 40, 50])
+def test_ddim_indexing_bit_exact_and_coefficients(golden, n):
+    s = _ddim()
+    s.set_timesteps(n)
+    g = golden["ddim"][str(n)]
+    assert s.timesteps.dtype == torch.int64
+    assert s.timesteps.tolist() == g["timesteps"]                       # integer indexing: bit-exact
+    assert s._prev_t[-1] == g["timesteps"][-1] - 1000 // n < 0          # last step falls back to final alpha
+    for i in range(n):
+        cx, ce, nxt = s.step_coefficients(i)
+        assert abs(cx - g["cx"][i]) <= 1e-6 * abs(g["cx"][i])           # alphas_cumprod is an fp32 table
+        assert abs(ce - g["ce"][i]) <= 1e-6 * max(abs(g["ce"][i]), 1e-3)
+        assert nxt == 1.0
+
+
+def test_ddim_config_round_trip_and_overrides():
+    s = _ddim()
+    c = s.config
+    assert c.beta_schedule == "linear" and c.steps_offset == 1 and c.clip_sample is False
+    assert c.set_alpha_to_one is False and c.beta_start == 0.00085 and c.beta_end == 0.012
+    assert abs(float(s.alphas_cumprod[999]) - 1.578962780e-03) < 1e-9
+    assert float(s.final_alpha_cumprod) == float(s.alphas_cumprod[0])
+    s2 = DDIMScheduler.from_config(s.config)
+    s2.set_timesteps(25)
+    assert s2.timesteps.tolist()[:3] == [961, 921, 881]
+    assert s.init_noise_sigma == 1.0 and s.order == 1
+    x = torch.randn(4)
+    assert s.scale_model_input(x, 961) is x
+    with pytest.raises(NotImplementedError):
+        DDIMScheduler.from_config(SD15_SCHEDULER_CONFIG, clip_sample=True)
+
+
+@pytest.mark.parametrize("n", [15, 25, 50])
+def test_euler_tables(golden, n):
+    s = EulerDiscreteScheduler.from_config(SD15_SCHEDULER_CONFIG, timestep_spacing="linspace", beta_schedule="linear")
+    s.set_timesteps(n)
+    g = golden["euler"][str(n)]
+    assert np.allclose(s.timesteps.numpy(), np.array(g["timesteps"], dtype=np.float32), rtol=0, atol=0)
+    assert np.allclose(s.sigmas.numpy(), np.array(g["sigmas"], dtype=np.float32), rtol=1e-7, atol=0)
+    assert abs(s.init_noise_sigma - max(g["sigmas"])) < 1e-6
+    sg = np.array(g["sigmas"], dtype=np.float64)
+    for i in range(n):
+        cx, ce, nxt = s.step_coefficients(i)
+        assert cx == 1.0 and abs(ce - (sg[i + 1] - sg[i])) < 1e-6
+        assert abs(nxt - 1.0 / np.sqrt(sg[i + 1] ** 2 + 1)) < 1e-6
+    assert abs(s.first_in_scale() - 1.0 / np.sqrt(sg[0] ** 2 + 1)) < 1e-7
+
+
+def test_step_rejects_unknown_timestep_and_missing_set_timesteps():
+    s = _ddim()
+    with pytest.raises(ValueError):
+        s.step(torch.zeros(1), 961, torch.zeros(1))
+    s.set_timesteps(25)
+    with pytest.raises(ValueError):
+        s._step_index_of(960)
+
+
+def _header_symbols():
+    src = open(os.path.join(ROOT, "include", "b200ad.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200ad_\w+)\s*\(", src)))
+
+
+def test_cabi_library_exports_every_declared_symbol():
+    syms = _header_symbols()
+    assert len(syms) >= 18
+    assert os.path.exists(lib.LIB_PATH), "libb200ad.so missing: run `python -c 'import __graft_entry__ as g; g.build()'`"
+    L = ctypes.CDLL(lib.LIB_PATH)
+    for s in syms:
+        assert hasattr(L, s), f"{s} declared in include/b200ad.h but not exported"
+    assert sorted(lib.SIGNATURES) == syms, "lib.py SIGNATURES and include/b200ad.h disagree"
+    assert lib.load().b200ad_version() >= 100
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback_anywhere():
+    from b200ad.ops import get_ops
+    from b200ad.pipeline import AnimateDiffPipeline
+    from b200ad.unet import UNetMotionConfig, UNetMotionModel
+    o = get_ops("fp32")
+    with pytest.raises(lib.B200ADError):
+        o.cfg_step(torch.zeros(4), torch.zeros(4), torch.zeros(4), 7.5, 1.0, 0.0)
+    with pytest.raises(RuntimeError):
+        AnimateDiffPipeline.from_pretrained("runwayml/stable-diffusion-v1-5")
+    m = UNetMotionModel(UNetMotionConfig(block_out_channels=(32, 64, 64, 64), norm_num_groups=8,
+                                         motion_norm_num_groups=8, num_attention_heads=2,
+                                         motion_num_attention_heads=2, cross_attention_dim=48))
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(1, 4, 4, 8, 8), 1, encoder_hidden_states=torch.zeros(1, 77, 48))
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "video-diffusion-experiments_b200")
+    for dp, _, fs in os.walk(pkg):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dp, f), errors="replace").read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f"{f} imports oracle/"
+
+
+def test_product_module_tree_matches_oracle_state_dict_keys():
+    from b200ad.unet import UNetMotionConfig, UNetMotionModel
+    from oracle.unet_motion import UNetMotionConfig as OC, UNetMotionModel as OM
+    with torch.device("meta"):
+        a, b = UNetMotionModel(UNetMotionConfig()), OM(OC())
+    ka, kb = a.state_dict(), b.state_dict()
+    assert set(ka) == set(kb)
+    assert all(ka[k].shape == kb[k].shape for k in ka)
+    assert sum(p.numel() for p in a.parameters()) == 1_312_730_244
+    names = dict(a.named_modules())
+    attn = names["down_blocks.0.attentions.0.transformer_blocks.0.attn1"]
+    assert type(attn).__name__ == "Attention" and attn.heads == 8 and attn.to_q.in_features == 320
+    assert len(a.attn_processors) == 32 + 21 * 2
+
+
+def test_diffusers_shim_import_surface():
+    sys.path.insert(0, os.path.join(ROOT, "compat"))
+    try:
+        import diffusers
+        from diffusers import AnimateDiffPipeline, DDIMScheduler as D, EulerDiscreteScheduler as E, MotionAdapter
+        from diffusers.utils import export_to_gif
+        assert callable(export_to_gif) and D is DDIMScheduler and E is EulerDiscreteScheduler
+        assert hasattr(AnimateDiffPipeline, "from_pretrained") and hasattr(MotionAdapter, "from_pretrained")
+        assert "b200ad" in diffusers.__version__
+    finally:
+        sys.path.remove(os.path.join(ROOT, "compat"))
+        for k in [k for k in sys.modules if k == "diffusers" or k.startswith("diffusers.")]:
+            del sys.modules[k]

@@ -165,8 +165,9 @@ class EulerDiscreteScheduler(_SchedulerBase):
             raise NotImplementedError("EulerDiscreteScheduler: only epsilon / linear interpolation is implemented")
         self.betas = _betas(c)
         self.alphas_cumprod = torch.cumprod(1.0 - self.betas, dim=0)
-        ac = self.alphas_cumprod.numpy().astype(np.float64)
-        self._base_sigmas = ((1 - ac) / ac) ** 0.5
+        # diffusers evaluates this in fp32 on the torch table, then interpolates in fp64 (np.interp)
+        ac = self.alphas_cumprod
+        self._base_sigmas = (((1 - ac) / ac) ** 0.5).numpy().astype(np.float64)
         self.sigmas = torch.from_numpy(np.concatenate([self._base_sigmas[::-1], [0.0]]).astype(np.float32))
         self._step_index = None
 
