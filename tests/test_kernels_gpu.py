@@ -196,7 +196,8 @@ def test_attention(mode, tol, nb, heads, Lq, Lk, d, dpad, kv_div):
 
 @pytest.mark.parametrize("mode,tol", MODES)
 @pytest.mark.parametrize("B,Fr,hw,C,heads", [(2, 16, 64, 320, 8), (1, 16, 16, 1280, 8), (2, 8, 9, 640, 8),
-                                             (1, 32, 4, 1280, 8), (2, 4, 16, 64, 8)])
+                                             (1, 32, 4, 1280, 8), (2, 4, 16, 64, 8), (1, 16, 5, 1280, 8),
+                                             (1, 20, 7, 320, 8)])
 def test_temporal_attention(mode, tol, B, Fr, hw, C, heads):
     o = ops(mode)
     d = C // heads

@@ -148,6 +148,9 @@ __global__ void temporal_attn_kernel(const T* __restrict__ qkv, int F, int hw, i
   }
 }
 
+int temporal_attention_bf16_mma(const bf16* qkv, int B, int F, int hw, int C, int heads, bf16* out,
+                                cudaStream_t st);   // temporal_mma.cu
+
 }  // namespace b200ad
 
 using namespace b200ad;
@@ -196,6 +199,8 @@ extern "C" int b200ad_temporal_attention(int op_dtype, const void* qkv, int B, i
   B200AD_REQUIRE(F >= 1 && F <= 32, "temporal_attention: F=%d (motion_max_seq_length is 32)", F);
   B200AD_REQUIRE(C % heads == 0 && (C / heads) % 2 == 0, "temporal_attention: C=%d heads=%d", C, heads);
   const int d = C / heads;
+  if (op_dtype == 0)
+    return temporal_attention_bf16_mma((const bf16*)qkv, B, F, hw, C, heads, (bf16*)out_op, (cudaStream_t)stream);
   int hpb = heads;
   auto smem_for = [&](int h) { return ((size_t)F * (3 * h * d + 1) + (size_t)h * F * F) * sizeof(float); };
   while (hpb > 1 && (smem_for(hpb) > 64 * 1024 || heads % hpb != 0)) --hpb;
