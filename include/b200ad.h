@@ -32,6 +32,10 @@ int b200ad_version(void);
 /* number of kernels launched by this library in this process since load (bench.py "gpu_launches") */
 long long b200ad_launch_count(void);
 
+/* diagnostics: device buffer of [grid][8] int64 cycle counters the GEMM kernel fills when non-NULL
+ * (producer total / wait-on-empty, UMMA issuer total / wait-on-full / wait-on-accumulator); NULL disables. */
+int b200ad_debug_buffer(void* dev_i64);
+
 /* ---- K2: Linear / 1x1 conv (replaces torch.nn.functional.linear / cuBLAS under diffusers
  * Attention.to_q/k/v/to_out, FeedForward, Transformer2DModel.proj_in/out, ResnetBlock2D.conv_shortcut).
  *   C[M,N] = A[M,K(lda)] * W[N,K]^T (+bias[N]) (+row_bias[(row/rb_div)*ld_rb + col]) (+residual[M,ld_res])

@@ -1,0 +1,35 @@
+#!/usr/bin/env python
+"""Where the tcgen05 GEMM's producer and UMMA-issuer threads wait (cycle counters written by the kernel itself):
+    python tools/gemm_waits.py"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import b200ad  # noqa
+from b200ad import lib
+from b200ad.ops import get_ops
+o = get_ops("bf16")
+L = lib.load()
+dbg = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")
+
+def run(name, fn):
+    for _ in range(2): fn()
+    L.b200ad_debug_buffer(dbg.data_ptr()); dbg.zero_()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+    L.b200ad_debug_buffer(None)
+    d = dbg.view(148, 8).double().cpu()
+    lead, peer = d[0::2], d[1::2]
+    print(f"{name}: {e0.elapsed_time(e1)*1e3:.1f} us | producer(leader) total {lead[:,0].mean():.0f} wait_empty {lead[:,1].mean():.0f} | "
+          f"producer(peer) total {peer[:,0].mean():.0f} wait_empty {peer[:,1].mean():.0f} | mma total {lead[:,2].mean():.0f} "
+          f"wait_full {lead[:,3].mean():.0f} wait_acc {lead[:,4].mean():.0f} | W-producer total {lead[:,5].mean():.0f} wait_empty {lead[:,6].mean():.0f}", flush=True)
+
+def bf(*s, scale=1.0): return (torch.randn(*s, device="cuda") * scale).to(torch.bfloat16)
+for (M, N, K) in [(8192, 8192, 8192), (131072, 320, 2880), (8192, 10240, 1280)]:
+    a, w = bf(M, K), bf(N, K, scale=K ** -0.5)
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    run(f"gemm {M}x{N}x{K} op", lambda: o.gemm(a, w, out_op=out))
+    print(f"   -> {2.0*M*N*K/1e12:.2f} TFLOP")
+for n, cin, cout, r in [(32, 320, 320, 64), (32, 1280, 1280, 16)]:
+    src, w = bf(n * r * r, cin), bf(cout, 9 * cin, scale=(9 * cin) ** -0.5)
+    run(f"conv {cin}->{cout}@{r}", lambda: o.conv3x3(src, w, n, r, r))

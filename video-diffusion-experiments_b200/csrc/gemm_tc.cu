@@ -1,244 +1,529 @@
 // tcgen05 GEMM / implicit-GEMM conv3x3 for sm_100a.
 //   C[M,N] = A[M,K] * W[N,K]^T, bf16 operands, fp32 accumulation in TMEM, fused fp32 epilogue.
-// Persistent, warp-specialised: warp 0 = TMA producer, warp 1 = UMMA issuer (+TMEM alloc),
-// warps 2..5 = epilogue (TMEM -> registers -> global).  Two TMEM accumulator stages so the epilogue
-// of tile i overlaps the mainloop of tile i+1.  Operand tiles are [rows x 64] bf16, 128-byte swizzle.
-// Conv mode loads the A tile with a 4-D tensor map over the NHWC image: one shifted box per filter
-// tap, out-of-bounds (halo) pixels zero-filled by TMA.
+//
+// CTA pair (cluster of 2, tcgen05 cta_group::2): one UMMA covers a 256 x BN output tile; each CTA stages its own
+// 128 rows of A and its own BN/2 rows of W, so every operand byte leaves L2 once per pair (the single-CTA version
+// of this kernel was bound by L2->SM operand traffic at ~49 % tensor-pipe activity, profiles/ncu_conv_r01b.md).
+// Persistent, warp-specialised:  warp 0 = TMA producer of A, warp 1 = TMA producer of W (issuing the two loads of a
+// stage from one thread made the producer the bottleneck: ~575 cycles per conv k-block against 320 cycles of UMMA
+// work, profiles/gemm_waits_r01.txt), warp 2 = UMMA issuer (leader CTA) + TMEM allocation,
+// warps 3..10 = epilogue in two groups of four warps that take alternate 32-column chunks of the tile.
+// Two TMEM accumulator stages: the epilogue of tile i overlaps the mainloop of tile i+1.
+// Epilogue data path: the fp32 residual chunk is fetched by TMA into swizzled smem ahead of time, each thread adds
+// its accumulator row (tcgen05.ld) + bias, the result is written back to smem and leaves through a TMA store --
+// no uncoalesced per-thread global traffic, and the bytes in flight per SM are set by the number of chunk buffers.
+// Conv mode loads the A tile with a 4-D tensor map over the NHWC image: one shifted box per filter tap,
+// out-of-bounds (halo) pixels zero-filled by TMA; outputs use the same 4-D box so the pixel tile maps back.
+#include <cooperative_groups.h>
+
 #include "gemm.cuh"
 #include "tmap.cuh"
 
 namespace b200ad {
 
-static constexpr int BM = 128;
+static constexpr int BM = 128;                      // rows per CTA (256 per pair)
 static constexpr int BK = 64;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KiB
-static constexpr int GEMM_THREADS = 192;
-static constexpr int SMEM_TILE_BUDGET = 192 * 1024;
+static constexpr int GEMM_THREADS = 352;
+static constexpr int EPI_THREADS = 256;
+static constexpr int F32_BUF_BYTES = 128 * 32 * 4;  // one [128 x 32] fp32 chunk, 128-byte rows, SWIZZLE_128B
+static constexpr int OP_BUF_BYTES = 128 * 32 * 2;   // one [128 x 32] bf16 chunk, 64-byte rows, SWIZZLE_64B
+static constexpr int MAX_STAGES = 8;
+static constexpr int MAX_NBUF = 4;
+static constexpr int SMEM_LIMIT = 232448;           // 227 KiB opt-in limit per CTA
 
 struct TcParams {
   int M, N, K;
-  int BN;
-  int num_stages;
-  int stage_bytes;
-  int num_m_tiles, num_n_tiles, num_kb;
+  int BN;                      // tile width of the pair (each CTA stages BN/2 rows of W)
+  int num_stages, stage_bytes;
+  int num_m_pairs, num_n_tiles, num_kb;
   int conv;
   int nimg, h, w;
   int n_box, h_box, w_box;
   int tiles_x, tiles_y;
   int cin_blocks;
   int tap_dy[9], tap_dx[9], tap_dn[9];
-  Epilogue epi;
+  // epilogue
+  int has_res, has_o32, has_oop, geglu;
+  int nbuf;                    // chunk buffers per epilogue group
+  int off_f32, off_op, off_bias, off_bars;   // smem offsets (from the 1024-aligned base)
+  const float* bias;
+  const float* row_bias;
+  int rb_div, ld_rb;
+  long long* dbg;              // optional [grid][8] cycle counters (b200ad_debug_buffer), null in production
 };
 
-__device__ __forceinline__ void epilogue_chunk(const TcParams& p, long long out_row, bool row_ok, int col0,
-                                               const uint32_t* acc) {
-  if (!row_ok || col0 >= p.N) return;
-  const Epilogue& e = p.epi;
-  if (e.geglu) {
-    // interleaved (h, g) pairs -> 16 outputs
-    bf16* out = reinterpret_cast<bf16*>(e.out_op) + out_row * e.ld_oop + (col0 >> 1);
-    uint32_t packed[8];
-#pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-      float add[4];
-      epilogue_load_addends(e, out_row, col0 + j, add);
-      float h0 = __uint_as_float(acc[j + 0]) + add[0];
-      float g0 = __uint_as_float(acc[j + 1]) + add[1];
-      float h1 = __uint_as_float(acc[j + 2]) + add[2];
-      float g1 = __uint_as_float(acc[j + 3]) + add[3];
-      packed[j >> 2] = pack_bf16x2(h0 * gelu_erf_f(g0), h1 * gelu_erf_f(g1));
-    }
-    uint4* o4 = reinterpret_cast<uint4*>(out);
-    o4[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-    o4[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `local_smem_addr` in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local_smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA loads of a CTA pair: data lands in this CTA's smem, the transaction bytes are reported to the mbarrier at
+// cluster address `bar` (the leader CTA's full barrier).
+__device__ __forceinline__ void tma2_load_2d(void* dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma2_load_4d(void* dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2,
+                                             int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+               "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish2() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma2_f16_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// all previously issued MMAs of this thread complete -> one arrive on the barrier at this smem offset in BOTH CTAs
+__device__ __forceinline__ void umma2_commit_mc(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__host__ __device__ __forceinline__ uint32_t umma_idesc_m(uint32_t m, uint32_t n, uint32_t ab_fmt) {
+  uint32_t d = 0;
+  d |= 1u << 4;               // c_format = F32
+  d |= ab_fmt << 7;           // a_format (1 = bf16)
+  d |= ab_fmt << 10;          // b_format
+  d |= (n >> 3) << 17;        // n_dim
+  d |= (m >> 4) << 24;        // m_dim
+  return d;
+}
+
+// Coordinates of one tile of this CTA.
+struct TileCoord {
+  int m_tile, n_tile;
+  int x0, y0, n0;
+};
+__device__ __forceinline__ TileCoord tile_coord(const TcParams& p, int tile, int rank) {
+  TileCoord t;
+  t.n_tile = tile % p.num_n_tiles;
+  t.m_tile = (tile / p.num_n_tiles) * 2 + rank;
+  t.x0 = t.y0 = t.n0 = 0;
+  if (p.conv) {
+    t.x0 = (t.m_tile % p.tiles_x) * p.w_box;
+    t.y0 = ((t.m_tile / p.tiles_x) % p.tiles_y) * p.h_box;
+    t.n0 = (t.m_tile / (p.tiles_x * p.tiles_y)) * p.n_box;
+  }
+  return t;
+}
+// accumulator columns per output chunk (a chunk is always 32 OUTPUT columns)
+__device__ __forceinline__ int acc_width(const TcParams& p) { return p.geglu ? 64 : 32; }
+__device__ __forceinline__ int tile_chunks(const TcParams& p, int n_tile) {
+  int cols = p.N - n_tile * p.BN;
+  if (cols > p.BN) cols = p.BN;
+  return cols / acc_width(p);
+}
+
+// Iterator over the chunks one epilogue group processes: tiles blockIdx-strided, chunks c = g, g+2, ...
+struct ChunkCursor {
+  int tile, c;
+};
+__device__ __forceinline__ void cursor_settle(const TcParams& p, ChunkCursor& cur, int g, int num_tiles, int stride) {
+  while (cur.tile < num_tiles && cur.c >= tile_chunks(p, cur.tile % p.num_n_tiles)) {
+    cur.tile += stride;
+    cur.c = g;
+  }
+}
+
+struct EpiMaps {
+  CUtensorMap res, o32, oop;
+};
+
+// Elected epilogue thread: make chunk buffer `buf` of group `g` ready for chunk `cur` (fetch its residual, or
+// just publish that the buffer is free).
+__device__ __forceinline__ void chunk_prefetch(const TcParams& p, const EpiMaps& em, uint8_t* f32buf, uint64_t* bar,
+                                               const ChunkCursor& cur, int rank) {
+  if (!p.has_res) {
+    mbar_arrive(bar);
     return;
   }
-  float v[32];
-#pragma unroll
-  for (int j = 0; j < 32; j += 4) {
-    float add[4];
-    epilogue_load_addends(e, out_row, col0 + j, add);
-    if (e.residual) {
-      float4 r = *reinterpret_cast<const float4*>(e.residual + out_row * e.ld_res + col0 + j);
-      add[0] += r.x; add[1] += r.y; add[2] += r.z; add[3] += r.w;
-    }
-    v[j + 0] = __uint_as_float(acc[j + 0]) + add[0];
-    v[j + 1] = __uint_as_float(acc[j + 1]) + add[1];
-    v[j + 2] = __uint_as_float(acc[j + 2]) + add[2];
-    v[j + 3] = __uint_as_float(acc[j + 3]) + add[3];
-  }
-  if (e.out_f32) {
-    float4* o = reinterpret_cast<float4*>(e.out_f32 + out_row * e.ld_o32 + col0);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-  }
-  if (e.out_op) {
-    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out_op) + out_row * e.ld_oop + col0);
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-      o[j] = make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                        pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
-  }
+  const TileCoord t = tile_coord(p, cur.tile, rank);
+  const int col0 = t.n_tile * p.BN + cur.c * 32;          // residual is never combined with geglu
+  mbar_arrive_expect_tx(bar, F32_BUF_BYTES);
+  if (p.conv) tma_load_4d(f32buf, &em.res, bar, col0, t.x0, t.y0, t.n0);
+  else tma_load_2d(f32buf, &em.res, bar, col0, t.m_tile * BM);
 }
 
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ TcParams p) {
+               const __grid_constant__ EpiMaps em, const __grid_constant__ TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)p.num_stages * p.stage_bytes);
-  uint64_t* full_bar = bars;                       // [num_stages]
-  uint64_t* empty_bar = bars + p.num_stages;       // [num_stages]
-  uint64_t* tfull_bar = bars + 2 * p.num_stages;   // [2]
-  uint64_t* tempty_bar = tfull_bar + 2;            // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.off_bars);
+  uint64_t* full_bar = bars;                            // [MAX_STAGES]  (used in the leader CTA)
+  uint64_t* empty_bar = full_bar + MAX_STAGES;          // [MAX_STAGES]  (both CTAs, signalled by multicast commit)
+  uint64_t* tfull_bar = empty_bar + MAX_STAGES;         // [2]           (both CTAs)
+  uint64_t* tempty_bar = tfull_bar + 2;                 // [2]           (leader; 16 remote/local warp arrivals)
+  uint64_t* res_full = tempty_bar + 2;                  // [2][MAX_NBUF] chunk buffer ready (per epilogue group)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 2 * MAX_NBUF);
+  float* sbias = reinterpret_cast<float*>(smem + p.off_bias);   // [2][256]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int rank = (int)cluster_ctarank();
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+  const int num_tiles = p.num_m_pairs * p.num_n_tiles;
   const uint32_t tmem_cols = (2 * p.BN <= 256) ? 256u : 512u;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (p.has_res) tma_prefetch_desc(&em.res);
+    if (p.has_o32) tma_prefetch_desc(&em.o32);
+    if (p.has_oop) tma_prefetch_desc(&em.oop);
     for (int s = 0; s < p.num_stages; ++s) {
-      mbar_init(&full_bar[s], 1);
+      mbar_init(&full_bar[s], 2);        // the leader's A producer and W producer each arrive with their tx bytes
       mbar_init(&empty_bar[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 4);     // one elected lane per epilogue warp
+      mbar_init(&tempty_bar[s], 16);
     }
+    for (int i = 0; i < 2 * MAX_NBUF; ++i) mbar_init(&res_full[i], 1);
     fence_barrier_init();
   }
-  if (warp == 1) {
-    tmem_alloc(tmem_slot, tmem_cols);
-    tmem_relinquish();
+  if (warp == 2) {
+    tmem_alloc2(tmem_slot, tmem_cols);
+    tmem_relinquish2();
   }
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();                    // barrier inits + TMEM allocation visible in both CTAs
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer of A (both CTAs; transaction bytes go to the leader's barrier) =====
+    // The whole warp runs the loop so that every operand of the TMA / UMMA instructions is warp-uniform (uniform
+    // registers); only the issue itself is predicated on one elected lane.  Issuing from inside an `if (lane == 0)`
+    // branch made ptxas wrap every UTMALDG / UTCHMMA in an ELECT + R2UR.BROADCAST loop (~100 cycles each).
+    {
       int stage = 0;
       uint32_t phase = 0;
-      const uint32_t tx_bytes = A_STAGE_BYTES + p.BN * BK * 2;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_tile = tile / p.num_n_tiles;
-        const int n_tile = tile % p.num_n_tiles;
-        int x0 = 0, y0 = 0, n0 = 0;
-        if (p.conv) {
-          x0 = (m_tile % p.tiles_x) * p.w_box;
-          y0 = ((m_tile / p.tiles_x) % p.tiles_y) * p.h_box;
-          n0 = (m_tile / (p.tiles_x * p.tiles_y)) * p.n_box;
-        }
+      const uint32_t fb0 = mapa_u32(smem_u32(&full_bar[0]), 0);
+      long long t_wait = 0;
+      const long long t_begin = clock64();
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const TileCoord t = tile_coord(p, tile, rank);
+        int tap = 0, cb = 0;
         for (int kb = 0; kb < p.num_kb; ++kb) {
+          const long long w0 = clock64();
           mbar_wait(&empty_bar[stage], phase ^ 1);
+          t_wait += clock64() - w0;
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
-          uint8_t* sb = sa + A_STAGE_BYTES;
-          mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-          if (p.conv) {
-            const int tap = kb / p.cin_blocks;
-            const int cb = kb - tap * p.cin_blocks;
-            tma_load_4d(sa, &tmA, &full_bar[stage], cb * BK, x0 + p.tap_dx[tap], y0 + p.tap_dy[tap],
-                        n0 + p.tap_dn[tap]);
-          } else {
-            tma_load_2d(sa, &tmA, &full_bar[stage], kb * BK, m_tile * BM);
+          if (elect_one()) {
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2u * A_STAGE_BYTES);
+            if (p.conv)
+              tma2_load_4d(sa, &tmA, fb0 + 8u * stage, cb * BK, t.x0 + p.tap_dx[tap], t.y0 + p.tap_dy[tap],
+                           t.n0 + p.tap_dn[tap]);
+            else
+              tma2_load_2d(sa, &tmA, fb0 + 8u * stage, kb * BK, t.m_tile * BM);
           }
-          tma_load_2d(sb, &tmB, &full_bar[stage], kb * BK, n_tile * p.BN);
+          __syncwarp();
+          if (p.conv && ++cb == p.cin_blocks) { cb = 0; ++tap; }
           if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
         }
       }
+      if (p.dbg && lane == 0) {
+        p.dbg[blockIdx.x * 8 + 0] = clock64() - t_begin;
+        p.dbg[blockIdx.x * 8 + 1] = t_wait;
+      }
     }
   } else if (warp == 1) {
-    // ===================== UMMA issuer =====================
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc((uint32_t)p.BN, false, 1u);
+    // ===================== TMA producer of W: this CTA's BN/2 rows of the tile =====================
+    {
+      int stage = 0;
+      uint32_t phase = 0;
+      const int half_bn = p.BN >> 1;
+      const uint32_t b_bytes = (uint32_t)(p.stage_bytes - A_STAGE_BYTES);
+      const uint32_t fb0 = mapa_u32(smem_u32(&full_bar[0]), 0);
+      long long t_wait = 0;
+      const long long t_begin = clock64();
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const int n_row = (tile % p.num_n_tiles) * p.BN + rank * half_bn;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          const long long w0 = clock64();
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          t_wait += clock64() - w0;
+          uint8_t* sb = smem + (size_t)stage * p.stage_bytes + A_STAGE_BYTES;
+          if (elect_one()) {
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2u * b_bytes);
+            tma2_load_2d(sb, &tmB, fb0 + 8u * stage, kb * BK, n_row);
+          }
+          __syncwarp();
+          if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+        }
+      }
+      if (p.dbg && lane == 0) {
+        p.dbg[blockIdx.x * 8 + 5] = clock64() - t_begin;
+        p.dbg[blockIdx.x * 8 + 6] = t_wait;
+      }
+    }
+  } else if (warp == 2) {
+    // ===================== UMMA issuer (leader CTA only) =====================
+    if (rank == 0) {
+      const uint32_t idesc = umma_idesc_m(256u, (uint32_t)p.BN, 1u);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      long long t_full = 0, t_tempty = 0;
+      const long long t_begin = clock64();
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
         const int as = it & 1;
+        const long long w0 = clock64();
         mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
+        t_tempty += clock64() - w0;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(as * p.BN);
         for (int kb = 0; kb < p.num_kb; ++kb) {
+          const long long w1 = clock64();
           mbar_wait(&full_bar[stage], phase);
+          t_full += clock64() - w1;
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
           const uint64_t adesc = umma_desc_k_sw128(sa);
           const uint64_t bdesc = umma_desc_k_sw128(sa + A_STAGE_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle atom: +2 in 16-byte units
-            umma_f16_ss(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                        (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle atom: +2 in 16-byte units
+              umma2_f16_ss(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                           (kb | k) != 0 ? 1u : 0u);
+            }
+            umma2_commit_mc(&empty_bar[stage]);
+            if (kb == p.num_kb - 1) umma2_commit_mc(&tfull_bar[as]);
           }
-          umma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[as]);
+      }
+      if (p.dbg && lane == 0) {
+        p.dbg[blockIdx.x * 8 + 2] = clock64() - t_begin;
+        p.dbg[blockIdx.x * 8 + 3] = t_full;
+        p.dbg[blockIdx.x * 8 + 4] = t_tempty;
       }
     }
   } else {
-    // ===================== epilogue warps (2..5) =====================
+    // ===================== epilogue: 2 groups x 4 warps =====================
+    const int ew = warp - 3;                     // 0..7
+    const int g = ew >> 2;                       // group: chunks c = g, g+2, ...
     const int quarter = warp & 3;                // TMEM lane quarter this warp may access
-    const int r_in_tile = quarter * 32 + lane;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int as = it & 1;
-      const int m_tile = tile / p.num_n_tiles;
-      const int n_tile = tile % p.num_n_tiles;
-      long long out_row;
-      bool row_ok;
-      if (p.conv) {
-        const int x = (m_tile % p.tiles_x) * p.w_box + (r_in_tile % p.w_box);
-        const int y = ((m_tile / p.tiles_x) % p.tiles_y) * p.h_box + ((r_in_tile / p.w_box) % p.h_box);
-        const int n = (m_tile / (p.tiles_x * p.tiles_y)) * p.n_box + r_in_tile / (p.w_box * p.h_box);
-        row_ok = (x < p.w) && (y < p.h) && (n < p.nimg);
-        out_row = ((long long)n * p.h + y) * p.w + x;
-      } else {
-        out_row = (long long)m_tile * BM + r_in_tile;
-        row_ok = out_row < p.M;
+    const int r = quarter * 32 + lane;           // row of the CTA tile owned by this thread
+    const int et = threadIdx.x - 96;             // 0..255
+    const bool lead_warp = (ew & 3) == 0;       // issues this group's TMA traffic (one elected lane)
+    const int AW = acc_width(p);
+    uint8_t* f32bufs = smem + p.off_f32 + (size_t)g * p.nbuf * F32_BUF_BYTES;
+    uint8_t* opbufs = smem + p.off_op + (size_t)g * p.nbuf * OP_BUF_BYTES;
+    uint64_t* rbar = res_full + g * MAX_NBUF;
+    const uint32_t tempty_remote = mapa_u32(smem_u32(&tempty_bar[0]), 0);
+
+    ChunkCursor pre;                             // prefetch cursor (elected thread only)
+    pre.tile = cluster_id;
+    pre.c = g;
+    if (lead_warp) {
+      cursor_settle(p, pre, g, num_tiles, num_clusters);
+      for (int b = 0; b < p.nbuf && pre.tile < num_tiles; ++b) {
+        if (elect_one()) chunk_prefetch(p, em, f32bufs + (size_t)b * F32_BUF_BYTES, &rbar[b], pre, rank);
+        __syncwarp();
+        pre.c += 2;
+        cursor_settle(p, pre, g, num_tiles, num_clusters);
       }
+    }
+    int k = 0;                                   // chunks processed by this group so far
+    int it = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
+      const int as = it & 1;
+      const TileCoord t = tile_coord(p, tile, rank);
+      const int nchunks = tile_chunks(p, t.n_tile);
+      // ---- bias (+ timestep-embedding row when it is the same for all rows of the tile) -> smem
+      long long out_row = 0;
+      bool rb_uniform = true;
+      if (p.row_bias) {
+        long long first, last;
+        if (p.conv) {
+          first = (long long)t.n0 * p.h * p.w;
+          int nl = t.n0 + p.n_box - 1;
+          if (nl > p.nimg - 1) nl = p.nimg - 1;
+          last = ((long long)nl + 1) * p.h * p.w - 1;
+          const int x = t.x0 + (r % p.w_box), y = t.y0 + ((r / p.w_box) % p.h_box);
+          int n = t.n0 + r / (p.w_box * p.h_box);
+          if (n > p.nimg - 1) n = p.nimg - 1;
+          out_row = ((long long)n * p.h + (y < p.h ? y : p.h - 1)) * p.w + (x < p.w ? x : p.w - 1);
+        } else {
+          first = (long long)t.m_tile * BM;
+          last = first + BM - 1;
+          if (last > p.M - 1) last = p.M - 1;
+          if (first > p.M - 1) first = p.M - 1;
+          out_row = first + r;
+          if (out_row > p.M - 1) out_row = p.M - 1;
+        }
+        rb_uniform = (first / p.rb_div) == (last / p.rb_div);
+      }
+      float* sb = sbias + (it & 1) * 256;
+      if (et < p.BN) {
+        const int col = t.n_tile * p.BN + et;
+        float v = 0.f;
+        if (col < p.N) {
+          if (p.bias) v = p.bias[col];
+          if (p.row_bias && rb_uniform) v += p.row_bias[(out_row / p.rb_div) * (long long)p.ld_rb + col];
+        }
+        sb[et] = v;
+      }
+      named_bar_sync(3, EPI_THREADS);
+      const float* rb_row =
+          (p.row_bias && !rb_uniform) ? p.row_bias + (out_row / p.rb_div) * (long long)p.ld_rb + t.n_tile * p.BN : nullptr;
+
       mbar_wait(&tfull_bar[as], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * p.BN);
-      for (int c = 0; c < p.BN; c += 32) {
-        uint32_t acc[32];
-        tmem_ld_32x32b_x32(taddr + (uint32_t)c, acc);
-        tmem_wait_ld();
-        epilogue_chunk(p, out_row, row_ok, n_tile * p.BN + c, acc);
+      for (int c = g; c < nchunks; c += 2, ++k) {
+        const int buf = k % p.nbuf;
+        uint8_t* fb = f32bufs + (size_t)buf * F32_BUF_BYTES;
+        uint8_t* ob = opbufs + (size_t)buf * OP_BUF_BYTES;
+        float v[32];
+        {
+          uint32_t acc[32];
+          tmem_ld_32x32b_x32(taddr + (uint32_t)(c * AW), acc);
+          tmem_wait_ld();
+          if (p.geglu) {
+            uint32_t acc2[32];
+            tmem_ld_32x32b_x32(taddr + (uint32_t)(c * AW + 32), acc2);
+            tmem_wait_ld();
+            const float* b = sb + c * 64;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              v[j] = (__uint_as_float(acc[2 * j]) + b[2 * j]) * gelu_erf_f(__uint_as_float(acc[2 * j + 1]) + b[2 * j + 1]);
+              v[16 + j] = (__uint_as_float(acc2[2 * j]) + b[32 + 2 * j]) *
+                          gelu_erf_f(__uint_as_float(acc2[2 * j + 1]) + b[32 + 2 * j + 1]);
+            }
+          } else {
+            const float* b = sb + c * 32;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]) + b[j];
+            if (rb_row) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                const float4 q = *reinterpret_cast<const float4*>(rb_row + c * 32 + j);
+                v[j] += q.x; v[j + 1] += q.y; v[j + 2] += q.z; v[j + 3] += q.w;
+              }
+            }
+          }
+        }
+        // the chunk buffer is free (its previous TMA store has read it) and holds the residual chunk if any
+        mbar_wait(&rbar[buf], (uint32_t)((k / p.nbuf) & 1));
+        if (p.has_res || p.has_o32) {
+          uint8_t* rowp = fb + r * 128;
+          const int sw = r & 7;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4* q = reinterpret_cast<float4*>(rowp + ((j ^ sw) << 4));
+            if (p.has_res) {
+              const float4 x = *q;
+              v[4 * j] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
+            }
+            if (p.has_o32) *q = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
+        }
+        if (p.has_oop) {
+          uint8_t* rowp = ob + r * 64;
+          const int sw = (r >> 1) & 3;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<uint4*>(rowp + ((j ^ sw) << 4)) =
+                make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                           pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1 + g, 128);
+        if (lead_warp) {
+          const int ocol = (t.n_tile * p.BN + c * AW) / (p.geglu ? 2 : 1);
+          if (lane == 0) {                       // bulk-group state is per thread: always the same lane
+            if (p.conv) {
+              if (p.has_o32) tma_store_4d(&em.o32, fb, ocol, t.x0, t.y0, t.n0);
+              if (p.has_oop) tma_store_4d(&em.oop, ob, ocol, t.x0, t.y0, t.n0);
+            } else {
+              if (p.has_o32) tma_store_2d(&em.o32, fb, ocol, t.m_tile * BM);
+              if (p.has_oop) tma_store_2d(&em.oop, ob, ocol, t.m_tile * BM);
+            }
+            tma_store_commit();
+            tma_store_wait_read0();
+            if (pre.tile < num_tiles) chunk_prefetch(p, em, fb, &rbar[buf], pre, rank);
+          }
+          __syncwarp();
+          if (pre.tile < num_tiles) {
+            pre.c += 2;
+            cursor_settle(p, pre, g, num_tiles, num_clusters);
+          }
+        }
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+      if (lane == 0) mbar_arrive_cluster(tempty_remote + (uint32_t)(as * 8));
     }
+    if (lead_warp && lane == 0) tma_store_wait_all();
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
+  cluster_sync_all();
+  if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, tmem_cols);
+    tmem_dealloc2(tmem_base, tmem_cols);
   }
 }
 
 // ----------------------------------------------------------------------------- host side
-static int pick_bn(int N, long long m_tiles, int num_sms) {
-  // Prefer wide tiles (smem bandwidth per MMA) unless that leaves SMs idle on small problems.
+static int g_num_sms = 0;
+static bool g_attr_set = false;
+static long long* g_dbg = nullptr;
+void set_gemm_debug_buffer(long long* p) { g_dbg = p; }
+
+static int pick_bn(int N, long long m_pairs, int num_clusters, bool geglu) {
+  // Prefer wide tiles (operand bytes per MMA) unless that leaves SM pairs idle on small problems.
   const int cands[4] = {256, 192, 160, 128};
   int best = 128;
   double best_cost = 1e30;
   for (int i = 0; i < 4; ++i) {
     const int bn = cands[i];
+    if (geglu && bn % 64 != 0) continue;
     const long long n_tiles = (N + bn - 1) / bn;
-    const long long tiles = m_tiles * n_tiles;
-    const long long waves = (tiles + num_sms - 1) / num_sms;
+    const long long tiles = m_pairs * n_tiles;
+    const long long waves = (tiles + num_clusters - 1) / num_clusters;
     // cost ~ waves * per-tile time (proportional to bn, with a fixed per-tile overhead), padded N included
     const double cost = (double)waves * (bn + 24.0);
     if (cost < best_cost - 1e-9) { best_cost = cost; best = bn; }
@@ -246,8 +531,22 @@ static int pick_bn(int N, long long m_tiles, int num_sms) {
   return best;
 }
 
-static int g_num_sms = 0;
-static bool g_attr_set = false;
+// Output / residual tensor map: dense [M, ld] rows, or the NHWC pixel box of a conv tile.  `elem` = 4 (fp32) or 2.
+static int make_out_map(CUtensorMap* tm, const void* ptr, long long ld, int ncols, int elem, const GemmArgs& a) {
+  const ConvGeom& g = a.conv;
+  const CUtensorMapDataType dt = elem == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const CUtensorMapSwizzle sw = elem == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  if (g.enabled) {
+    uint64_t dims[4] = {(uint64_t)ncols, (uint64_t)g.w, (uint64_t)g.h, (uint64_t)g.nimg};
+    uint64_t str[3] = {(uint64_t)ld * elem, (uint64_t)g.w * ld * elem, (uint64_t)g.h * g.w * ld * elem};
+    uint32_t box[4] = {32u, (uint32_t)g.w_box, (uint32_t)g.h_box, (uint32_t)g.n_box};
+    return make_tmap(tm, dt, ptr, 4, dims, str, box, sw);
+  }
+  uint64_t dims[2] = {(uint64_t)ncols, (uint64_t)a.M};
+  uint64_t str[1] = {(uint64_t)ld * elem};
+  uint32_t box[2] = {32u, (uint32_t)BM};
+  return make_tmap(tm, dt, ptr, 2, dims, str, box, sw);
+}
 
 int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   B200AD_REQUIRE(a.M > 0 && a.N > 0 && a.K > 0, "gemm: empty problem M=%d N=%d K=%d", a.M, a.N, a.K);
@@ -258,12 +557,28 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     B200AD_CHECK_CUDA(cudaGetDevice(&dev));
     B200AD_CHECK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   }
+  const Epilogue& e = a.epi;
   TcParams p;
   memset(&p, 0, sizeof(p));
   p.M = a.M; p.N = a.N; p.K = a.K;
-  p.epi = a.epi;
+  p.has_res = e.residual != nullptr;
+  p.has_o32 = e.out_f32 != nullptr;
+  p.has_oop = e.out_op != nullptr;
+  p.geglu = e.geglu;
+  p.dbg = g_dbg;
+  p.bias = e.bias; p.row_bias = e.row_bias; p.rb_div = e.rb_div > 0 ? e.rb_div : 1; p.ld_rb = e.ld_rb;
+  if (e.geglu) {
+    B200AD_REQUIRE(e.out_op && !e.out_f32 && !e.residual && !e.row_bias, "geglu epilogue writes out_op only");
+    B200AD_REQUIRE(a.N % 64 == 0, "geglu: N=%d must be a multiple of 64", a.N);
+  }
+  if (e.residual) B200AD_REQUIRE(e.ld_res % 4 == 0, "gemm: residual leading dimension %lld not a multiple of 4", e.ld_res);
+  if (e.out_f32) B200AD_REQUIRE(e.ld_o32 % 4 == 0, "gemm: out_f32 leading dimension %lld not a multiple of 4", e.ld_o32);
+  if (e.out_op) B200AD_REQUIRE(e.ld_oop % 8 == 0, "gemm: out_op leading dimension %lld not a multiple of 8", e.ld_oop);
   CUtensorMap tmA, tmB;
+  EpiMaps em;
+  memset(&em, 0, sizeof(em));
   const ConvGeom& g = a.conv;
+  int num_m_tiles;
   if (g.enabled) {
     B200AD_REQUIRE(g.cin % BK == 0, "conv: cin=%d must be a multiple of %d on the tcgen05 path", g.cin, BK);
     B200AD_REQUIRE(g.n_box * g.h_box * g.w_box == BM, "conv: tile box %dx%dx%d != %d rows", g.n_box, g.h_box,
@@ -275,7 +590,7 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     p.n_box = g.n_box; p.h_box = g.h_box; p.w_box = g.w_box;
     p.tiles_x = (g.w + g.w_box - 1) / g.w_box;
     p.tiles_y = (g.h + g.h_box - 1) / g.h_box;
-    p.num_m_tiles = p.tiles_x * p.tiles_y * ((g.nimg + g.n_box - 1) / g.n_box);
+    num_m_tiles = p.tiles_x * p.tiles_y * ((g.nimg + g.n_box - 1) / g.n_box);
     p.cin_blocks = g.cin / BK;
     for (int t = 0; t < 9; ++t) { p.tap_dy[t] = g.tap_dy[t]; p.tap_dx[t] = g.tap_dx[t]; p.tap_dn[t] = g.tap_dn[t]; }
     uint64_t dims[4] = {(uint64_t)g.cin, (uint64_t)g.src_w, (uint64_t)g.src_h, (uint64_t)g.src_nimg};
@@ -283,35 +598,65 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     uint32_t box[4] = {(uint32_t)BK, (uint32_t)g.w_box, (uint32_t)g.h_box, (uint32_t)g.n_box};
     if (int rc = make_tmap_bf16(&tmA, a.A, 4, dims, strides, box)) return rc;
   } else {
-    p.num_m_tiles = (a.M + BM - 1) / BM;
+    num_m_tiles = (a.M + BM - 1) / BM;
     uint64_t dims[2] = {(uint64_t)a.K, (uint64_t)a.M};
     uint64_t strides[1] = {(uint64_t)a.lda * 2};
     uint32_t box[2] = {(uint32_t)BK, (uint32_t)BM};
     if (int rc = make_tmap_bf16(&tmA, a.A, 2, dims, strides, box)) return rc;
   }
-  p.BN = pick_bn(a.N, p.num_m_tiles, g_num_sms);
-  if (a.epi.geglu) B200AD_REQUIRE(a.epi.out_op && !a.epi.out_f32 && !a.epi.residual, "geglu epilogue writes out_op only");
+  p.num_m_pairs = (num_m_tiles + 1) / 2;
+  const int max_clusters = g_num_sms / 2;
+  p.BN = pick_bn(a.N, p.num_m_pairs, max_clusters, e.geglu != 0);
   p.num_n_tiles = (a.N + p.BN - 1) / p.BN;
   p.num_kb = (a.K + BK - 1) / BK;
-  p.stage_bytes = A_STAGE_BYTES + p.BN * BK * 2;
-  p.num_stages = SMEM_TILE_BUDGET / p.stage_bytes;
-  if (p.num_stages > 8) p.num_stages = 8;
+  p.stage_bytes = A_STAGE_BYTES + (p.BN / 2) * BK * 2;
   {
     uint64_t dims[2] = {(uint64_t)a.K, (uint64_t)a.N};
     uint64_t strides[1] = {(uint64_t)a.K * 2};
-    uint32_t box[2] = {(uint32_t)BK, (uint32_t)p.BN};
+    uint32_t box[2] = {(uint32_t)BK, (uint32_t)(p.BN / 2)};
     if (int rc = make_tmap_bf16(&tmB, a.W, 2, dims, strides, box)) return rc;
   }
-  const size_t smem_bytes = (size_t)p.num_stages * p.stage_bytes + 1024 /*align*/ + 256 /*barriers*/;
+  const int n_out = e.geglu ? a.N / 2 : a.N;
+  if (p.has_res) if (int rc = make_out_map(&em.res, e.residual, e.ld_res, n_out, 4, a)) return rc;
+  if (p.has_o32) if (int rc = make_out_map(&em.o32, e.out_f32, e.ld_o32, n_out, 4, a)) return rc;
+  if (p.has_oop) if (int rc = make_out_map(&em.oop, e.out_op, e.ld_oop, n_out, 2, a)) return rc;
+  // ---- shared memory plan: mainloop stages first, the rest goes to epilogue chunk buffers (bytes in flight)
+  const int per_buf = ((p.has_res || p.has_o32) ? F32_BUF_BYTES : 0) + (p.has_oop ? OP_BUF_BYTES : 0);
+  const int fixed = 2 * 256 * 4 + 512;                       // bias staging + barriers
+  const int budget = SMEM_LIMIT - 1024 - fixed;
+  int want_stages = p.num_kb < 6 ? (p.num_kb < 3 ? 3 : p.num_kb) : 6;
+  p.nbuf = MAX_NBUF;
+  while (p.nbuf > 2 && want_stages * p.stage_bytes + 2 * p.nbuf * per_buf > budget) --p.nbuf;
+  p.num_stages = (budget - 2 * p.nbuf * per_buf) / p.stage_bytes;
+  if (p.num_stages > MAX_STAGES) p.num_stages = MAX_STAGES;
+  B200AD_REQUIRE(p.num_stages >= 2, "gemm: shared memory plan failed (BN=%d)", p.BN);
+  p.off_f32 = p.num_stages * p.stage_bytes;
+  p.off_op = p.off_f32 + ((p.has_res || p.has_o32) ? 2 * p.nbuf * F32_BUF_BYTES : 0);
+  p.off_bias = p.off_op + (p.has_oop ? 2 * p.nbuf * OP_BUF_BYTES : 0);
+  p.off_bars = p.off_bias + 2 * 256 * 4;
+  const size_t smem_bytes = (size_t)p.off_bars + 512 + 1024 /*align*/;
+  B200AD_REQUIRE(smem_bytes <= (size_t)SMEM_LIMIT, "gemm: %zu bytes of shared memory", smem_bytes);
   if (!g_attr_set) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     g_attr_set = true;
   }
-  const long long tiles = (long long)p.num_m_tiles * p.num_n_tiles;
-  const int grid = (int)(tiles < g_num_sms ? tiles : g_num_sms);
-  gemm_tc_kernel<<<grid, GEMM_THREADS, smem_bytes, stream>>>(tmA, tmB, p);
+  const long long tiles = (long long)p.num_m_pairs * p.num_n_tiles;
+  const int clusters = (int)(tiles < max_clusters ? tiles : max_clusters);
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(2 * clusters);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel, tmA, tmB, em, p));
   count_launch();
-  B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 

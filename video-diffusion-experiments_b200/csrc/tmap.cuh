@@ -12,10 +12,9 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 
 EncodeTiledFn get_encode_tiled();   // api.cu
 
-// bf16 tensor, innermost dim contiguous.  dims/box innermost-first; strides_bytes for dims 1..rank-1.
-inline int make_tmap_bf16(CUtensorMap* out, const void* gptr, int rank, const uint64_t* dims,
-                          const uint64_t* strides_bytes, const uint32_t* box,
-                          CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
+// Tiled tensor map, innermost dim contiguous.  dims/box innermost-first; strides_bytes for dims 1..rank-1.
+inline int make_tmap(CUtensorMap* out, CUtensorMapDataType dtype, const void* gptr, int rank, const uint64_t* dims,
+                     const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz) {
   EncodeTiledFn fn = get_encode_tiled();
   B200AD_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
   B200AD_REQUIRE((reinterpret_cast<uintptr_t>(gptr) & 15) == 0, "TMA base pointer must be 16-byte aligned");
@@ -34,11 +33,22 @@ inline int make_tmap_bf16(CUtensorMap* out, const void* gptr, int rank, const ui
     B200AD_REQUIRE((strides_bytes[i] & 15) == 0, "TMA stride %d = %llu not a multiple of 16 bytes", i,
                    (unsigned long long)strides_bytes[i]);
   }
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(gptr),
+  CUresult r = fn(out, dtype, (cuuint32_t)rank, const_cast<void*>(gptr),
                   gdim, gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B200AD_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return 0;
+}
+
+inline int make_tmap_bf16(CUtensorMap* out, const void* gptr, int rank, const uint64_t* dims,
+                          const uint64_t* strides_bytes, const uint32_t* box,
+                          CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
+  return make_tmap(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, gptr, rank, dims, strides_bytes, box, swz);
+}
+inline int make_tmap_f32(CUtensorMap* out, const void* gptr, int rank, const uint64_t* dims,
+                         const uint64_t* strides_bytes, const uint32_t* box,
+                         CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
+  return make_tmap(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, gptr, rank, dims, strides_bytes, box, swz);
 }
 
 }  // namespace b200ad

@@ -22,6 +22,7 @@ SIGNATURES = {
     "b200ad_last_error": [],
     "b200ad_version": [],
     "b200ad_launch_count": [],
+    "b200ad_debug_buffer": [_P],
     "b200ad_gemm": [_I, _P, _L, _P, _I, _I, _I, _P, _P, _I, _I, _P, _L, _P, _L, _P, _L, _I, _P],
     "b200ad_conv3x3": [_I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _I, _I, _P, _L, _P, _L, _P, _L, _P],
     "b200ad_gn_nblk": [_I],
