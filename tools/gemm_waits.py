@@ -10,7 +10,7 @@ from b200ad import lib
 from b200ad.ops import get_ops
 o = get_ops("bf16")
 L = lib.load()
-dbg = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")
+dbg = torch.zeros(148 * 16, dtype=torch.int64, device="cuda")
 
 def run(name, fn):
     for _ in range(2): fn()
@@ -18,14 +18,14 @@ def run(name, fn):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); fn(); e1.record(); torch.cuda.synchronize()
     L.b200ad_debug_buffer(None)
-    d = dbg.view(148, 8).double().cpu()
+    d = dbg.view(148, 16).double().cpu()
     lead, peer = d[0::2], d[1::2]
     print(f"{name}: {e0.elapsed_time(e1)*1e3:.1f} us | producer(leader) total {lead[:,0].mean():.0f} wait_empty {lead[:,1].mean():.0f} | "
           f"producer(peer) total {peer[:,0].mean():.0f} wait_empty {peer[:,1].mean():.0f} | mma total {lead[:,2].mean():.0f} "
-          f"wait_full {lead[:,3].mean():.0f} wait_acc {lead[:,4].mean():.0f} | W-producer total {lead[:,5].mean():.0f} wait_empty {lead[:,6].mean():.0f}", flush=True)
+          f"wait_full {lead[:,3].mean():.0f} wait_acc {lead[:,4].mean():.0f} | W-producer total {lead[:,5].mean():.0f} wait_empty {lead[:,6].mean():.0f}\n      epilogue(g0 lead warp): total {lead[:,8].mean():.0f} wait_tfull {lead[:,9].mean():.0f} wait_buf {lead[:,10].mean():.0f} | io warp total {lead[:,7].mean():.0f} wait_chunk {lead[:,11].mean():.0f} issue {lead[:,15].mean():.0f} wait_read {lead[:,12].mean():.0f} | bias_stage {lead[:,13].mean():.0f} chunks {lead[:,14].mean():.0f}", flush=True)
 
 def bf(*s, scale=1.0): return (torch.randn(*s, device="cuda") * scale).to(torch.bfloat16)
-for (M, N, K) in [(8192, 8192, 8192), (131072, 320, 2880), (8192, 10240, 1280)]:
+for (M, N, K) in [(8192, 8192, 8192), (131072, 960, 320), (8192, 10240, 1280)]:
     a, w = bf(M, K), bf(N, K, scale=K ** -0.5)
     out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
     run(f"gemm {M}x{N}x{K} op", lambda: o.gemm(a, w, out_op=out))
@@ -33,3 +33,14 @@ for (M, N, K) in [(8192, 8192, 8192), (131072, 320, 2880), (8192, 10240, 1280)]:
 for n, cin, cout, r in [(32, 320, 320, 64), (32, 1280, 1280, 16)]:
     src, w = bf(n * r * r, cin), bf(cout, 9 * cin, scale=(9 * cin) ** -0.5)
     run(f"conv {cin}->{cout}@{r}", lambda: o.conv3x3(src, w, n, r, r))
+
+M, N, K = 131072, 320, 320
+a, w = bf(M, K), bf(N, K, scale=K ** -0.5)
+res = torch.randn(M, N, device="cuda")
+bias = torch.randn(N, device="cuda")
+run("gemm 131072x320x320 res32 in place", lambda: o.gemm(a, w, bias=bias, residual=res, out_f32=res))
+M, N, K = 131072, 2560, 320
+a, w = bf(M, K), bf(N, K, scale=K ** -0.5)
+bias = torch.randn(N, device="cuda")
+out = torch.empty(M, N // 2, device="cuda", dtype=torch.bfloat16)
+run("gemm 131072x2560x320 geglu", lambda: o.gemm(a, w, bias=bias, out_op=out, geglu=True))

@@ -7,7 +7,9 @@
 // Persistent, warp-specialised:  warp 0 = TMA producer of A, warp 1 = TMA producer of W (issuing the two loads of a
 // stage from one thread made the producer the bottleneck: ~575 cycles per conv k-block against 320 cycles of UMMA
 // work, profiles/gemm_waits_r01.txt), warp 2 = UMMA issuer (leader CTA) + TMEM allocation,
-// warps 3..10 = epilogue in two groups of four warps that take alternate 32-column chunks of the tile.
+// warps 3..10 = epilogue math in two groups of four warps that take alternate 32-column chunks of the tile,
+// warp 11 = epilogue I/O: TMA stores of finished chunks, buffer recycling and residual prefetch, so the math warps
+// never wait for a store to drain and never block-synchronise (chunk hand-off is mbarrier arrive/wait only).
 // Two TMEM accumulator stages: the epilogue of tile i overlaps the mainloop of tile i+1.
 // Epilogue data path: the fp32 residual chunk is fetched by TMA into swizzled smem ahead of time, each thread adds
 // its accumulator row (tcgen05.ld) + bias, the result is written back to smem and leaves through a TMA store --
@@ -24,13 +26,21 @@ namespace b200ad {
 static constexpr int BM = 128;                      // rows per CTA (256 per pair)
 static constexpr int BK = 64;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KiB
-static constexpr int GEMM_THREADS = 352;
+static constexpr int GEMM_THREADS = 384;
 static constexpr int EPI_THREADS = 256;
 static constexpr int F32_BUF_BYTES = 128 * 32 * 4;  // one [128 x 32] fp32 chunk, 128-byte rows, SWIZZLE_128B
 static constexpr int OP_BUF_BYTES = 128 * 32 * 2;   // one [128 x 32] bf16 chunk, 64-byte rows, SWIZZLE_64B
 static constexpr int MAX_STAGES = 8;
 static constexpr int MAX_NBUF = 4;
 static constexpr int SMEM_LIMIT = 232448;           // 227 KiB opt-in limit per CTA
+
+// Cycle counters for tools/gemm_waits.py: compiled in only with -DB200AD_GEMM_PROFILE (reading the clock a dozen
+// times per chunk is itself a measurable cost in the epilogue loops).
+#ifdef B200AD_GEMM_PROFILE
+__device__ __forceinline__ long long prof_clock() { return clock64(); }
+#else
+__device__ __forceinline__ long long prof_clock() { return 0; }
+#endif
 
 struct TcParams {
   int M, N, K;
@@ -50,7 +60,7 @@ struct TcParams {
   const float* bias;
   const float* row_bias;
   int rb_div, ld_rb;
-  long long* dbg;              // optional [grid][8] cycle counters (b200ad_debug_buffer), null in production
+  long long* dbg;              // optional [grid][16] cycle counters (b200ad_debug_buffer), null in production
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -147,18 +157,42 @@ __device__ __forceinline__ int acc_width(const TcParams& p) { return p.geglu ? 6
 __device__ __forceinline__ int tile_chunks(const TcParams& p, int n_tile) {
   int cols = p.N - n_tile * p.BN;
   if (cols > p.BN) cols = p.BN;
-  return cols / acc_width(p);
+  return cols >> (p.geglu ? 6 : 5);
 }
 
 // Iterator over the chunks one epilogue group processes: tiles blockIdx-strided, chunks c = g, g+2, ...
+// The tile's coordinates are cached so the integer divisions happen once per tile, not once per chunk.
 struct ChunkCursor {
-  int tile, c;
+  int tile, c, nchunks;
+  TileCoord t;
 };
-__device__ __forceinline__ void cursor_settle(const TcParams& p, ChunkCursor& cur, int g, int num_tiles, int stride) {
-  while (cur.tile < num_tiles && cur.c >= tile_chunks(p, cur.tile % p.num_n_tiles)) {
+__device__ __forceinline__ void cursor_load(const TcParams& p, ChunkCursor& cur, int num_tiles, int rank) {
+  if (cur.tile < num_tiles) {
+    cur.t = tile_coord(p, cur.tile, rank);
+    cur.nchunks = tile_chunks(p, cur.t.n_tile);
+  }
+}
+__device__ __forceinline__ void cursor_settle(const TcParams& p, ChunkCursor& cur, int g, int num_tiles, int stride,
+                                              int rank) {
+  while (cur.tile < num_tiles && cur.c >= cur.nchunks) {
     cur.tile += stride;
     cur.c = g;
+    cursor_load(p, cur, num_tiles, rank);
   }
+}
+
+// explicit shared-space accesses (the aligned dynamic-smem base is an integer-derived generic pointer: plain
+// dereferences compile to generic LD.E / ST.E)
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_f4(uint32_t a, float x, float y, float z, float w) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+__device__ __forceinline__ void sts_u4(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
 
 struct EpiMaps {
@@ -173,11 +207,43 @@ __device__ __forceinline__ void chunk_prefetch(const TcParams& p, const EpiMaps&
     mbar_arrive(bar);
     return;
   }
-  const TileCoord t = tile_coord(p, cur.tile, rank);
+  const TileCoord& t = cur.t;
   const int col0 = t.n_tile * p.BN + cur.c * 32;          // residual is never combined with geglu
   mbar_arrive_expect_tx(bar, F32_BUF_BYTES);
   if (p.conv) tma_load_4d(f32buf, &em.res, bar, col0, t.x0, t.y0, t.n0);
   else tma_load_2d(f32buf, &em.res, bar, col0, t.m_tile * BM);
+}
+
+// Per-group state of the epilogue I/O warp.
+struct IoGroup {
+  uint8_t* f32;            // this group's fp32 chunk buffers
+  uint8_t* op;             // this group's bf16 staging buffers
+  uint64_t* ready;         // res_full barriers of the group
+  uint64_t* cdone;         // chunk_done barriers of the group
+  int buf, prev_buf;       // buffer of the chunk being stored / of the previous chunk (the next one to recycle)
+  uint32_t phase;
+  ChunkCursor pre;         // next chunk whose buffer has not been handed out yet
+};
+__device__ __forceinline__ void io_group_init(const TcParams& p, const EpiMaps& em, IoGroup& G, int g, uint8_t* smem,
+                                              uint64_t* res_full, uint64_t* chunk_done, int cluster_id,
+                                              int num_tiles, int num_clusters, int rank, bool io_lane) {
+  G.f32 = smem + p.off_f32 + (size_t)g * p.nbuf * F32_BUF_BYTES;
+  G.op = smem + p.off_op + (size_t)g * p.nbuf * OP_BUF_BYTES;
+  G.ready = res_full + g * MAX_NBUF;
+  G.cdone = chunk_done + g * MAX_NBUF;
+  G.buf = 0;
+  G.prev_buf = p.nbuf - 1;           // the one buffer not handed out below
+  G.phase = 0;
+  G.pre.tile = cluster_id;
+  G.pre.c = g;
+  cursor_load(p, G.pre, num_tiles, rank);
+  cursor_settle(p, G.pre, g, num_tiles, num_clusters, rank);
+  for (int b = 0; b < p.nbuf - 1 && G.pre.tile < num_tiles; ++b) {
+    if (io_lane) chunk_prefetch(p, em, G.f32 + (size_t)b * F32_BUF_BYTES, &G.ready[b], G.pre, rank);
+    __syncwarp();
+    G.pre.c += 2;
+    cursor_settle(p, G.pre, g, num_tiles, num_clusters, rank);
+  }
 }
 
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -191,7 +257,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tfull_bar = empty_bar + MAX_STAGES;         // [2]           (both CTAs)
   uint64_t* tempty_bar = tfull_bar + 2;                 // [2]           (leader; 16 remote/local warp arrivals)
   uint64_t* res_full = tempty_bar + 2;                  // [2][MAX_NBUF] chunk buffer ready (per epilogue group)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + 2 * MAX_NBUF);
+  uint64_t* chunk_done = res_full + 2 * MAX_NBUF;       // [2][MAX_NBUF] chunk written to smem by its 128 threads
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(chunk_done + 2 * MAX_NBUF);
   float* sbias = reinterpret_cast<float*>(smem + p.off_bias);   // [2][256]
 
   const int warp = threadIdx.x >> 5;
@@ -216,7 +283,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], 16);
     }
-    for (int i = 0; i < 2 * MAX_NBUF; ++i) mbar_init(&res_full[i], 1);
+    for (int i = 0; i < 2 * MAX_NBUF; ++i) {
+      mbar_init(&res_full[i], 1);
+      mbar_init(&chunk_done[i], 128);
+    }
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -238,14 +308,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       const uint32_t fb0 = mapa_u32(smem_u32(&full_bar[0]), 0);
       long long t_wait = 0;
-      const long long t_begin = clock64();
+      const long long t_begin = prof_clock();
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         const TileCoord t = tile_coord(p, tile, rank);
         int tap = 0, cb = 0;
         for (int kb = 0; kb < p.num_kb; ++kb) {
-          const long long w0 = clock64();
+          const long long w0 = prof_clock();
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          t_wait += clock64() - w0;
+          t_wait += prof_clock() - w0;
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
           if (elect_one()) {
             if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2u * A_STAGE_BYTES);
@@ -261,8 +331,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       if (p.dbg && lane == 0) {
-        p.dbg[blockIdx.x * 8 + 0] = clock64() - t_begin;
-        p.dbg[blockIdx.x * 8 + 1] = t_wait;
+        p.dbg[blockIdx.x * 16 + 0] = prof_clock() - t_begin;
+        p.dbg[blockIdx.x * 16 + 1] = t_wait;
       }
     }
   } else if (warp == 1) {
@@ -274,13 +344,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t b_bytes = (uint32_t)(p.stage_bytes - A_STAGE_BYTES);
       const uint32_t fb0 = mapa_u32(smem_u32(&full_bar[0]), 0);
       long long t_wait = 0;
-      const long long t_begin = clock64();
+      const long long t_begin = prof_clock();
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         const int n_row = (tile % p.num_n_tiles) * p.BN + rank * half_bn;
         for (int kb = 0; kb < p.num_kb; ++kb) {
-          const long long w0 = clock64();
+          const long long w0 = prof_clock();
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          t_wait += clock64() - w0;
+          t_wait += prof_clock() - w0;
           uint8_t* sb = smem + (size_t)stage * p.stage_bytes + A_STAGE_BYTES;
           if (elect_one()) {
             if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2u * b_bytes);
@@ -291,8 +361,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       if (p.dbg && lane == 0) {
-        p.dbg[blockIdx.x * 8 + 5] = clock64() - t_begin;
-        p.dbg[blockIdx.x * 8 + 6] = t_wait;
+        p.dbg[blockIdx.x * 16 + 5] = prof_clock() - t_begin;
+        p.dbg[blockIdx.x * 16 + 6] = t_wait;
       }
     }
   } else if (warp == 2) {
@@ -303,18 +373,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       int it = 0;
       long long t_full = 0, t_tempty = 0;
-      const long long t_begin = clock64();
+      const long long t_begin = prof_clock();
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
         const int as = it & 1;
-        const long long w0 = clock64();
+        const long long w0 = prof_clock();
         mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
-        t_tempty += clock64() - w0;
+        t_tempty += prof_clock() - w0;
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(as * p.BN);
         for (int kb = 0; kb < p.num_kb; ++kb) {
-          const long long w1 = clock64();
+          const long long w1 = prof_clock();
           mbar_wait(&full_bar[stage], phase);
-          t_full += clock64() - w1;
+          t_full += prof_clock() - w1;
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)stage * p.stage_bytes);
           const uint64_t adesc = umma_desc_k_sw128(sa);
@@ -334,10 +404,72 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       if (p.dbg && lane == 0) {
-        p.dbg[blockIdx.x * 8 + 2] = clock64() - t_begin;
-        p.dbg[blockIdx.x * 8 + 3] = t_full;
-        p.dbg[blockIdx.x * 8 + 4] = t_tempty;
+        p.dbg[blockIdx.x * 16 + 2] = prof_clock() - t_begin;
+        p.dbg[blockIdx.x * 16 + 3] = t_full;
+        p.dbg[blockIdx.x * 16 + 4] = t_tempty;
       }
+    }
+  } else if (warp == 11) {
+    // ===================== epilogue I/O warp =====================
+    // Walks the chunks of this CTA in tile order (chunk c belongs to math group c & 1).  For each: wait until the
+    // group's 128 threads have written it, issue its TMA store(s), and once the store of the group's previous chunk
+    // has drained hand that buffer to the chunk nbuf-1 ahead (fetch its residual / publish that it is free).
+    // All per-group state lives in scalars (no indexed arrays, no divisions: this loop is the epilogue's pacemaker).
+    const bool io_lane = elect_one();
+    const int AW = acc_width(p);
+    const int nbuf = p.nbuf;
+    IoGroup G0, G1;
+    io_group_init(p, em, G0, 0, smem, res_full, chunk_done, cluster_id, num_tiles, num_clusters, rank, io_lane);
+    io_group_init(p, em, G1, 1, smem, res_full, chunk_done, cluster_id, num_tiles, num_clusters, rank, io_lane);
+    int last_g = -1;
+    long long io_wait_done = 0, io_wait_read = 0, io_issue = 0;
+    const long long io_begin = prof_clock();
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      const TileCoord t = tile_coord(p, tile, rank);
+      const int nchunks = tile_chunks(p, t.n_tile);
+      const int ocol0 = (t.n_tile * p.BN) >> (p.geglu ? 1 : 0);
+      for (int c = 0; c < nchunks; ++c) {
+        const int g = c & 1;
+        IoGroup& G = g ? G1 : G0;
+        const long long i0 = prof_clock();
+        mbar_wait(&G.cdone[G.buf], G.phase);
+        const long long i1 = prof_clock();
+        io_wait_done += i1 - i0;
+        if (io_lane) {
+          uint8_t* fb = G.f32 + (size_t)G.buf * F32_BUF_BYTES;
+          uint8_t* ob = G.op + (size_t)G.buf * OP_BUF_BYTES;
+          const int ocol = ocol0 + c * 32;
+          if (p.conv) {
+            if (p.has_o32) tma_store_4d(&em.o32, fb, ocol, t.x0, t.y0, t.n0);
+            if (p.has_oop) tma_store_4d(&em.oop, ob, ocol, t.x0, t.y0, t.n0);
+          } else {
+            if (p.has_o32) tma_store_2d(&em.o32, fb, ocol, t.m_tile * BM);
+            if (p.has_oop) tma_store_2d(&em.oop, ob, ocol, t.m_tile * BM);
+          }
+          tma_store_commit();
+          const long long i2 = prof_clock();
+          io_issue += i2 - i1;
+          // the store of this group's previous chunk is the 2nd (or, at an odd tile boundary, the 1st) most recent
+          if (last_g == g) tma_store_wait_read1(); else tma_store_wait_read2();
+          io_wait_read += prof_clock() - i2;
+          if (G.pre.tile < num_tiles)
+            chunk_prefetch(p, em, G.f32 + (size_t)G.prev_buf * F32_BUF_BYTES, &G.ready[G.prev_buf], G.pre, rank);
+        }
+        __syncwarp();
+        if (G.pre.tile < num_tiles) {
+          G.pre.c += 2;
+          cursor_settle(p, G.pre, g, num_tiles, num_clusters, rank);
+        }
+        G.prev_buf = G.buf;
+        if (++G.buf == nbuf) { G.buf = 0; G.phase ^= 1u; }
+        last_g = g;
+      }
+    }
+    (void)AW;
+    if (io_lane) tma_store_wait_all();
+    if (p.dbg && io_lane) {
+      long long* d = p.dbg + blockIdx.x * 16;
+      d[7] = prof_clock() - io_begin; d[11] = io_wait_done; d[12] = io_wait_read; d[15] = io_issue;
     }
   } else {
     // ===================== epilogue: 2 groups x 4 warps =====================
@@ -346,27 +478,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int quarter = warp & 3;                // TMEM lane quarter this warp may access
     const int r = quarter * 32 + lane;           // row of the CTA tile owned by this thread
     const int et = threadIdx.x - 96;             // 0..255
-    const bool lead_warp = (ew & 3) == 0;       // issues this group's TMA traffic (one elected lane)
     const int AW = acc_width(p);
     uint8_t* f32bufs = smem + p.off_f32 + (size_t)g * p.nbuf * F32_BUF_BYTES;
     uint8_t* opbufs = smem + p.off_op + (size_t)g * p.nbuf * OP_BUF_BYTES;
     uint64_t* rbar = res_full + g * MAX_NBUF;
+    uint64_t* cdone = chunk_done + g * MAX_NBUF;
     const uint32_t tempty_remote = mapa_u32(smem_u32(&tempty_bar[0]), 0);
-
-    ChunkCursor pre;                             // prefetch cursor (elected thread only)
-    pre.tile = cluster_id;
-    pre.c = g;
-    if (lead_warp) {
-      cursor_settle(p, pre, g, num_tiles, num_clusters);
-      for (int b = 0; b < p.nbuf && pre.tile < num_tiles; ++b) {
-        if (elect_one()) chunk_prefetch(p, em, f32bufs + (size_t)b * F32_BUF_BYTES, &rbar[b], pre, rank);
-        __syncwarp();
-        pre.c += 2;
-        cursor_settle(p, pre, g, num_tiles, num_clusters);
-      }
-    }
     int k = 0;                                   // chunks processed by this group so far
+    int buf = 0;                                 // chunk buffer of chunk k, and its barrier phase
+    uint32_t bphase = 0;
     int it = 0;
+    long long e_tfull = 0, e_rbar = 0, e_bar = 0, e_store = 0, e_bias = 0;
+    const long long e_begin = prof_clock();
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
       const int as = it & 1;
       const TileCoord t = tile_coord(p, tile, rank);
@@ -396,6 +519,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         rb_uniform = (first / p.rb_div) == (last / p.rb_div);
       }
       float* sb = sbias + (it & 1) * 256;
+      const long long q0 = prof_clock();
       if (et < p.BN) {
         const int col = t.n_tile * p.BN + et;
         float v = 0.f;
@@ -403,17 +527,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (p.bias) v = p.bias[col];
           if (p.row_bias && rb_uniform) v += p.row_bias[(out_row / p.rb_div) * (long long)p.ld_rb + col];
         }
-        sb[et] = v;
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_u32(sb + et)), "f"(v) : "memory");
       }
       named_bar_sync(3, EPI_THREADS);
       const float* rb_row =
           (p.row_bias && !rb_uniform) ? p.row_bias + (out_row / p.rb_div) * (long long)p.ld_rb + t.n_tile * p.BN : nullptr;
 
+      const long long q1 = prof_clock();
+      e_bias += q1 - q0;
       mbar_wait(&tfull_bar[as], (it >> 1) & 1);
+      e_tfull += prof_clock() - q1;
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * p.BN);
       for (int c = g; c < nchunks; c += 2, ++k) {
-        const int buf = k % p.nbuf;
         uint8_t* fb = f32bufs + (size_t)buf * F32_BUF_BYTES;
         uint8_t* ob = opbufs + (size_t)buf * OP_BUF_BYTES;
         float v[32];
@@ -421,21 +547,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           uint32_t acc[32];
           tmem_ld_32x32b_x32(taddr + (uint32_t)(c * AW), acc);
           tmem_wait_ld();
+          const uint32_t sb_a = smem_u32(sb) + (uint32_t)(c * AW * 4);
           if (p.geglu) {
             uint32_t acc2[32];
             tmem_ld_32x32b_x32(taddr + (uint32_t)(c * AW + 32), acc2);
             tmem_wait_ld();
-            const float* b = sb + c * 64;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              v[j] = (__uint_as_float(acc[2 * j]) + b[2 * j]) * gelu_erf_f(__uint_as_float(acc[2 * j + 1]) + b[2 * j + 1]);
-              v[16 + j] = (__uint_as_float(acc2[2 * j]) + b[32 + 2 * j]) *
-                          gelu_erf_f(__uint_as_float(acc2[2 * j + 1]) + b[32 + 2 * j + 1]);
+            for (int j = 0; j < 8; ++j) {
+              const float4 b0 = lds_f4(sb_a + 16 * j), b1 = lds_f4(sb_a + 128 + 16 * j);
+              v[2 * j] = (__uint_as_float(acc[4 * j]) + b0.x) * gelu_erf_f(__uint_as_float(acc[4 * j + 1]) + b0.y);
+              v[2 * j + 1] = (__uint_as_float(acc[4 * j + 2]) + b0.z) * gelu_erf_f(__uint_as_float(acc[4 * j + 3]) + b0.w);
+              v[16 + 2 * j] = (__uint_as_float(acc2[4 * j]) + b1.x) * gelu_erf_f(__uint_as_float(acc2[4 * j + 1]) + b1.y);
+              v[17 + 2 * j] =
+                  (__uint_as_float(acc2[4 * j + 2]) + b1.z) * gelu_erf_f(__uint_as_float(acc2[4 * j + 3]) + b1.w);
             }
           } else {
-            const float* b = sb + c * 32;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]) + b[j];
+            for (int j = 0; j < 8; ++j) {
+              const float4 b = lds_f4(sb_a + 16 * j);
+              v[4 * j] = __uint_as_float(acc[4 * j]) + b.x;
+              v[4 * j + 1] = __uint_as_float(acc[4 * j + 1]) + b.y;
+              v[4 * j + 2] = __uint_as_float(acc[4 * j + 2]) + b.z;
+              v[4 * j + 3] = __uint_as_float(acc[4 * j + 3]) + b.w;
+            }
             if (rb_row) {
 #pragma unroll
               for (int j = 0; j < 32; j += 4) {
@@ -446,57 +580,44 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
         // the chunk buffer is free (its previous TMA store has read it) and holds the residual chunk if any
-        mbar_wait(&rbar[buf], (uint32_t)((k / p.nbuf) & 1));
+        const long long q2 = prof_clock();
+        mbar_wait(&rbar[buf], bphase);
+        e_rbar += prof_clock() - q2;
         if (p.has_res || p.has_o32) {
-          uint8_t* rowp = fb + r * 128;
+          const uint32_t rowa = smem_u32(fb) + (uint32_t)(r * 128);
           const int sw = r & 7;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            float4* q = reinterpret_cast<float4*>(rowp + ((j ^ sw) << 4));
+            const uint32_t qa = rowa + (uint32_t)((j ^ sw) << 4);
             if (p.has_res) {
-              const float4 x = *q;
+              const float4 x = lds_f4(qa);
               v[4 * j] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
             }
-            if (p.has_o32) *q = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            if (p.has_o32) sts_f4(qa, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
           }
         }
         if (p.has_oop) {
-          uint8_t* rowp = ob + r * 64;
+          const uint32_t rowa = smem_u32(ob) + (uint32_t)(r * 64);
           const int sw = (r >> 1) & 3;
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            *reinterpret_cast<uint4*>(rowp + ((j ^ sw) << 4)) =
-                make_uint4(pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                           pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+            sts_u4(rowa + (uint32_t)((j ^ sw) << 4), pack_bf16x2(v[8 * j], v[8 * j + 1]),
+                   pack_bf16x2(v[8 * j + 2], v[8 * j + 3]), pack_bf16x2(v[8 * j + 4], v[8 * j + 5]),
+                   pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
         }
-        fence_proxy_async_smem();
-        named_bar_sync(1 + g, 128);
-        if (lead_warp) {
-          const int ocol = (t.n_tile * p.BN + c * AW) / (p.geglu ? 2 : 1);
-          if (lane == 0) {                       // bulk-group state is per thread: always the same lane
-            if (p.conv) {
-              if (p.has_o32) tma_store_4d(&em.o32, fb, ocol, t.x0, t.y0, t.n0);
-              if (p.has_oop) tma_store_4d(&em.oop, ob, ocol, t.x0, t.y0, t.n0);
-            } else {
-              if (p.has_o32) tma_store_2d(&em.o32, fb, ocol, t.m_tile * BM);
-              if (p.has_oop) tma_store_2d(&em.oop, ob, ocol, t.m_tile * BM);
-            }
-            tma_store_commit();
-            tma_store_wait_read0();
-            if (pre.tile < num_tiles) chunk_prefetch(p, em, fb, &rbar[buf], pre, rank);
-          }
-          __syncwarp();
-          if (pre.tile < num_tiles) {
-            pre.c += 2;
-            cursor_settle(p, pre, g, num_tiles, num_clusters);
-          }
-        }
+        fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store
+        mbar_arrive(&cdone[buf]);
+        if (++buf == p.nbuf) { buf = 0; bphase ^= 1u; }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(tempty_remote + (uint32_t)(as * 8));
     }
-    if (lead_warp && lane == 0) tma_store_wait_all();
+    if (p.dbg && ew == 0 && lane == 0) {
+      long long* d = p.dbg + blockIdx.x * 16;
+      d[8] = prof_clock() - e_begin; d[9] = e_tfull; d[10] = e_rbar; d[13] = e_bias;
+      d[14] = k;
+    }
   }
 
   tc_fence_before();
