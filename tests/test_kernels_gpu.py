@@ -173,7 +173,8 @@ def _attn_ref(q, k, v):
 @pytest.mark.parametrize("nb,heads,Lq,Lk,d,dpad,kv_div", [
     (2, 8, 256, 256, 40, 64, 1), (3, 2, 1024, 1024, 40, 64, 1), (2, 8, 64, 64, 160, 192, 1),
     (2, 4, 256, 256, 80, 128, 1), (4, 8, 256, 77, 40, 64, 2), (2, 8, 64, 77, 160, 192, 2),
-    (1, 2, 200, 300, 8, 64, 1), (2, 8, 1024, 77, 80, 128, 1)])
+    (1, 2, 200, 300, 8, 64, 1), (2, 8, 1024, 77, 80, 128, 1), (2, 2, 1024, 1024, 80, 128, 1),
+    (1, 2, 512, 512, 40, 64, 1), (1, 1, 2304, 2304, 80, 128, 1), (1, 2, 768, 768, 24, 64, 1)])
 def test_attention(mode, tol, nb, heads, Lq, Lk, d, dpad, kv_div):
     o = ops(mode)
     nkv = nb // kv_div
@@ -192,6 +193,26 @@ def test_attention(mode, tol, nb, heads, Lq, Lk, d, dpad, kv_div):
     kvd = torch.cat([pack(k, Lk, nkv), pack(v, Lk, nkv)], -1).to(DEV, o.op_dtype)   # fused (k|v) buffer
     out = o.attention(qd, kvd[:, :heads * dpad], kvd[:, heads * dpad:], nb, heads, Lq, Lk, d, dpad, kv_div)
     assert rel(out.cpu(), ref) < tol
+
+
+@pytest.mark.parametrize("d,dpad", [(40, 64), (80, 128)])
+def test_attention_lazy_rescale_with_growing_maxima(d, dpad):
+    """Ping-pong kernel (attn_fa.cu): scores with a wide range and maxima that keep growing along the key axis, so
+    the lazy O rescale (threshold 2^8) fires several times; compared with fp32 SDPA."""
+    o = ops("bf16")
+    nb, heads, L = 1, 2, 1024
+    q = bf(rnd(nb, heads, L, d, seed=11) * 3.0)
+    k = bf(rnd(nb, heads, L, d, seed=12) * (1.0 + 3.0 * torch.arange(L)[None, None, :, None] / L))
+    v = bf(rnd(nb, heads, L, d, seed=13))
+    ref = _attn_ref(q, k, v).permute(0, 2, 1, 3).reshape(nb * L, heads * d)
+
+    def pack(t):
+        p = torch.zeros(nb, L, heads, dpad)
+        p[..., :d] = t.permute(0, 2, 1, 3)
+        return p.reshape(nb * L, heads * dpad).to(DEV, torch.bfloat16)
+
+    out = o.attention(pack(q), pack(k), pack(v), nb, heads, L, L, d, dpad, 1)
+    assert rel(out.cpu(), ref) < 1e-2
 
 
 @pytest.mark.parametrize("mode,tol", MODES)

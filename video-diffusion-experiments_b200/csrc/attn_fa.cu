@@ -1,0 +1,323 @@
+// Ping-pong tcgen05 flash attention for the long spatial self-attention layers (L = 4096 / 1024 at 512^2,
+// 9216 / 2304 at 768^2; head width 40 or 80).
+//   O = softmax(Q K^T / sqrt(d)) V per (frame-image n, head); bf16 operands, fp32 S / O accumulators in TMEM.
+// One CTA owns TWO query tiles of 128 rows (A and B) of one (n, head) and walks the keys in tiles of BN:
+//   warp 0      TMA producer: Q_A, Q_B once, then K_j / V_j through a ring of NST stages
+//   warp 1      UMMA issuer:  S_A(j)=Q_A K_j^T, S_B(j)=Q_B K_j^T, O_A+=P_A(j)V_j, O_B+=P_B(j)V_j, ordered so that the
+//               tensor pipe works on tile B while the softmax threads of tile A are busy, and vice versa
+//   warps 2..5  softmax of tile A, warps 6..9 softmax of tile B: one thread per query row; the whole score row is
+//               held in registers (tcgen05.ld), exp2 with the running maximum, bf16 P written to swizzled smem
+// The layers this kernel serves are bound by the exponential (128 x 128 exp2 per 2.6 MFLOP of useful MMA at d=40),
+// so the structure aims at keeping both softmax groups busy all the time:
+//   * the O accumulator is rescaled lazily -- only when a row maximum grew by more than 2^8 since the last
+//     rescale (FlashAttention-4's trick); P then stays <= 256, well inside bf16/fp32 range;
+//   * QK^T only contracts over ceil(d/16) k-steps (the head-width padding columns are zero).
+#include "../../include/b200ad.h"
+#include "tmap.cuh"
+
+namespace b200ad {
+
+static constexpr int FA_THREADS = 320;
+
+struct FaParams {
+  int Lq, Lk, d, nkv;
+  int dk16;                // k-steps of 16 for Q K^T
+  float scale_log2;        // d^-1/2 * log2(e)
+  bf16* out;
+  long long ldo;
+};
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// DP: padded head width (64 or 128).  BN: keys per tile (128 for DP=64, 64 for DP=128).
+template <int DP, int BN>
+__global__ void __launch_bounds__(FA_THREADS, 1)
+attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+               const __grid_constant__ CUtensorMap tmV, const __grid_constant__ FaParams p) {
+  constexpr int NS = DP / 64;                    // 64-column slabs per operand row
+  constexpr int NST = 3;                         // K/V ring depth
+  constexpr int QSLAB = 128 * 128;               // [128 rows x 64 bf16]
+  constexpr int KSLAB = BN * 128;                // [BN rows x 64 bf16]
+  constexpr int PS = BN / 64;                    // P slabs (each [128 q rows x 64 keys])
+  constexpr uint32_t S_COL0 = 0, S_COL1 = BN, O_COL0 = 2 * BN, O_COL1 = 2 * BN + DP;
+  constexpr uint32_t TMEM_COLS = 512;
+  static_assert(2 * BN + 2 * DP <= 512, "TMEM budget");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                                  // [2][NS] slabs
+  uint8_t* sK = sQ + 2 * NS * QSLAB;                   // [NST][NS]
+  uint8_t* sV = sK + NST * NS * KSLAB;                 // [NST][NS]
+  uint8_t* sP = sV + NST * NS * KSLAB;                 // [2][PS]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * PS * QSLAB);
+  uint64_t* q_full = bars;                             // [1]
+  uint64_t* kv_full = bars + 1;                        // [NST]
+  uint64_t* kv_empty = kv_full + NST;                  // [NST]
+  uint64_t* s_full = kv_empty + NST;                   // [2]
+  uint64_t* p_full = s_full + 2;                       // [2]  128 arrivals
+  uint64_t* o_full = p_full + 2;                       // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int qt = blockIdx.x, hd = blockIdx.y, n = blockIdx.z;     // qt: pair of 128-row query tiles
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < NST; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_full[s], 128); mbar_init(&o_full[s], 1); }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (whole warp loops; one elected lane issues) =====================
+    if (elect_one()) {
+      mbar_arrive_expect_tx(q_full, 2 * NS * QSLAB);
+#pragma unroll
+      for (int t = 0; t < 2; ++t)
+#pragma unroll
+        for (int s = 0; s < NS; ++s)
+          tma_load_3d(sQ + (t * NS + s) * QSLAB, &tmQ, q_full, hd * DP + s * 64, (2 * qt + t) * 128, n);
+    }
+    __syncwarp();
+    int st = 0;
+    uint32_t ph = 0;
+    for (int j = 0; j < p.nkv; ++j) {
+      mbar_wait(&kv_empty[st], ph ^ 1);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&kv_full[st], 2 * NS * KSLAB);
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+          tma_load_3d(sK + (st * NS + s) * KSLAB, &tmK, &kv_full[st], hd * DP + s * 64, j * BN, n);
+          tma_load_3d(sV + (st * NS + s) * KSLAB, &tmV, &kv_full[st], hd * DP + s * 64, j * BN, n);
+        }
+      }
+      __syncwarp();
+      if (++st == NST) { st = 0; ph ^= 1; }
+    }
+  } else if (warp == 1) {
+    // ===================== UMMA issuer =====================
+    const uint32_t idesc_s = umma_idesc((uint32_t)BN, false, 1u);
+    const uint32_t idesc_o = umma_idesc((uint32_t)DP, true, 1u);
+    const uint32_t sQ_a = smem_u32(sQ), sK_a = smem_u32(sK), sV_a = smem_u32(sV), sP_a = smem_u32(sP);
+    // S_t = Q_t K^T for the K tile in ring stage `st`
+    auto issue_s = [&](int t, int st) {
+      if (elect_one()) {
+        for (int kk = 0; kk < p.dk16; ++kk) {
+          const uint64_t adesc = umma_desc_k_sw128(sQ_a + (uint32_t)((t * NS + (kk >> 2)) * QSLAB)) + (uint64_t)(2 * (kk & 3));
+          const uint64_t bdesc = umma_desc_k_sw128(sK_a + (uint32_t)((st * NS + (kk >> 2)) * KSLAB)) + (uint64_t)(2 * (kk & 3));
+          umma_f16_ss(tmem_base + (t ? S_COL1 : S_COL0), adesc, bdesc, idesc_s, kk > 0 ? 1u : 0u);
+        }
+        umma_commit(&s_full[t]);
+      }
+      __syncwarp();
+    };
+    // O_t (+)= P_t V for the V tile in ring stage `st`; 16 keys per instruction
+    auto issue_pv = [&](int t, int st, bool first, bool release_kv) {
+      if (elect_one()) {
+#pragma unroll
+        for (int kk = 0; kk < BN / 16; ++kk) {
+          const uint64_t adesc = umma_desc_k_sw128(sP_a + (uint32_t)((t * PS + (kk >> 2)) * QSLAB)) + (uint64_t)(2 * (kk & 3));
+          const uint64_t bdesc = umma_desc_mn_sw128(sV_a + (uint32_t)(st * NS * KSLAB + kk * 2048), (uint32_t)KSLAB);
+          umma_f16_ss(tmem_base + (t ? O_COL1 : O_COL0), adesc, bdesc, idesc_o, (first && kk == 0) ? 0u : 1u);
+        }
+        umma_commit(&o_full[t]);
+        if (release_kv) umma_commit(&kv_empty[st]);
+      }
+      __syncwarp();
+    };
+    mbar_wait(q_full, 0);
+    mbar_wait(&kv_full[0], 0);
+    tc_fence_after();
+    issue_s(0, 0);
+    issue_s(1, 0);
+    int st = 0;
+    uint32_t ph = 0;
+    for (int j = 0; j < p.nkv; ++j) {
+      int st_n = st + 1;
+      uint32_t ph_n = ph;
+      if (st_n == NST) { st_n = 0; ph_n ^= 1; }
+      const bool more = (j + 1 < p.nkv);
+      if (more) mbar_wait(&kv_full[st_n], ph_n);
+      // tile A: P_A(j) is in smem (and S_A has been read) -> O_A += P_A V_j, then S_A(j+1)
+      mbar_wait(&p_full[0], j & 1);
+      tc_fence_after();
+      issue_pv(0, st, j == 0, false);
+      if (more) issue_s(0, st_n);
+      // tile B
+      mbar_wait(&p_full[1], j & 1);
+      tc_fence_after();
+      issue_pv(1, st, j == 0, true);
+      if (more) issue_s(1, st_n);
+      st = st_n;
+      ph = ph_n;
+    }
+  } else {
+    // ===================== softmax: warps 2..5 -> tile A, warps 6..9 -> tile B; one thread per query row ====
+    const int t = (warp - 2) >> 2;
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+    const uint32_t s_tmem = tmem_base + lane_addr + (t ? S_COL1 : S_COL0);
+    const uint32_t o_tmem = tmem_base + lane_addr + (t ? O_COL1 : O_COL0);
+    const uint32_t p_row = smem_u32(sP + t * PS * QSLAB) + (uint32_t)(row * 128);
+    const int sw = row & 7;
+    const float sc = p.scale_log2;
+    float m_used = -INFINITY;       // maximum (scaled, log2 units) the stored O / l are relative to
+    float l = 0.f;
+    for (int j = 0; j < p.nkv; ++j) {
+      mbar_wait(&s_full[t], j & 1);
+      tc_fence_after();
+      float s[BN];
+#pragma unroll
+      for (int c = 0; c < BN; c += 32) tmem_ld_32x32b_x32(s_tmem + c, reinterpret_cast<uint32_t*>(s + c));
+      tmem_wait_ld();
+      const int kbase = j * BN;
+      if (kbase + BN > p.Lk) {
+#pragma unroll
+        for (int i = 0; i < BN; ++i)
+          if (kbase + i >= p.Lk) s[i] = -INFINITY;
+      }
+      float mx = s[0];
+#pragma unroll
+      for (int i = 1; i < BN; ++i) mx = fmaxf(mx, s[i]);
+      mx *= sc;
+      // lazy rescale: keep the old reference maximum unless this row's maximum grew by more than 2^8
+      const bool need = mx > m_used + 8.0f;
+      const float m_new = need ? mx : m_used;
+      const float neg_m = -m_new;
+      float sum = 0.f;
+#pragma unroll
+      for (int i = 0; i < BN; ++i) {
+        s[i] = fast_exp2(fmaf(s[i], sc, neg_m));
+        sum += s[i];
+      }
+      // PV(j-1) must be complete before P is overwritten or O rescaled
+      if (j > 0) {
+        mbar_wait(&o_full[t], (j - 1) & 1);
+        tc_fence_after();
+      }
+      if (__any_sync(0xffffffffu, need) && j > 0) {
+        const float alpha = need ? fast_exp2(m_used - m_new) : 1.0f;
+#pragma unroll 1
+        for (int c = 0; c < DP; c += 32) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(o_tmem + c, r);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+          tmem_st_32x32b_x32(o_tmem + c, r);
+        }
+        tmem_wait_st();
+        l *= alpha;
+      }
+      m_used = m_new;
+      l += sum;
+      // bf16 P row -> swizzled smem: 8 keys per 16-byte chunk, chunk index XOR (row & 7) inside each 64-key slab
+#pragma unroll
+      for (int c8 = 0; c8 < BN / 8; ++c8) {
+        const int slab = c8 >> 3, chunk = (c8 & 7) ^ sw;
+        const uint32_t a = p_row + (uint32_t)(slab * QSLAB + chunk * 16);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(s[8 * c8], s[8 * c8 + 1])),
+                     "r"(pack_bf16x2(s[8 * c8 + 2], s[8 * c8 + 3])), "r"(pack_bf16x2(s[8 * c8 + 4], s[8 * c8 + 5])),
+                     "r"(pack_bf16x2(s[8 * c8 + 6], s[8 * c8 + 7]))
+                     : "memory");
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(&p_full[t]);
+    }
+    // ---- epilogue: O / l -> bf16 ----
+    mbar_wait(&o_full[t], (p.nkv - 1) & 1);
+    tc_fence_after();
+    const float inv = 1.f / l;
+    const int qrow = (2 * qt + t) * 128 + row;
+    bf16* orow = p.out + ((long long)n * p.Lq + qrow) * p.ldo + hd * p.d;
+#pragma unroll 1
+    for (int c = 0; c < DP; c += 32) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(o_tmem + c, r);
+      tmem_wait_ld();
+      if (qrow < p.Lq) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          if (c + i < p.d)
+            *reinterpret_cast<uint32_t*>(orow + c + i) =
+                pack_bf16x2(__uint_as_float(r[i]) * inv, __uint_as_float(r[i + 1]) * inv);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+template <int DP, int BN>
+static int launch_attn_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                          int nbatch, int heads, int L, int d, void* out, long long ldo, cudaStream_t stream) {
+  constexpr int NS = DP / 64;
+  CUtensorMap tmQ, tmK, tmV;
+  uint64_t dims[3] = {(uint64_t)heads * DP, (uint64_t)L, (uint64_t)nbatch};
+  {
+    uint64_t str[2] = {(uint64_t)ldq * 2, (uint64_t)L * ldq * 2};
+    uint32_t box[3] = {64, 128, 1};
+    if (int rc = make_tmap_bf16(&tmQ, q, 3, dims, str, box)) return rc;
+  }
+  {
+    uint32_t box[3] = {64, (uint32_t)BN, 1};
+    uint64_t strk[2] = {(uint64_t)ldk * 2, (uint64_t)L * ldk * 2};
+    if (int rc = make_tmap_bf16(&tmK, k, 3, dims, strk, box)) return rc;
+    uint64_t strv[2] = {(uint64_t)ldv * 2, (uint64_t)L * ldv * 2};
+    if (int rc = make_tmap_bf16(&tmV, v, 3, dims, strv, box)) return rc;
+  }
+  FaParams p;
+  p.Lq = L; p.Lk = L; p.d = d;
+  p.nkv = (L + BN - 1) / BN;
+  p.dk16 = (d + 15) / 16;
+  p.scale_log2 = 1.4426950408889634f / sqrtf((float)d);
+  p.out = reinterpret_cast<bf16*>(out);
+  p.ldo = ldo;
+  const size_t smem = (size_t)(2 * NS * 128 * 128 + 2 * 3 * NS * BN * 128 + 2 * (BN / 64) * 128 * 128) + 1024 + 256;
+  static bool attr = false;
+  if (!attr) {
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr = true;
+  }
+  dim3 grid(L / 256, heads, nbatch);
+  attn_fa_kernel<DP, BN><<<grid, FA_THREADS, smem, stream>>>(tmQ, tmK, tmV, p);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Self-attention fast path; returns 1 when the shape is not served here (the caller falls back to attn_tc.cu).
+int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                      int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, void* out, long long ldo,
+                      cudaStream_t stream) {
+  if (Lq != Lk || kv_div != 1 || Lq % 256 != 0 || Lq < 512) return 1;
+  if (dpad == 64) return launch_attn_fa<64, 128>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
+  if (dpad == 128) return launch_attn_fa<128, 64>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
+  return 1;
+}
+
+}  // namespace b200ad

@@ -14,6 +14,10 @@ int attention_f32_simt(const float* q, long long ldq, const float* k, long long 
                        int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, float* out, long long ldo,
                        cudaStream_t stream);   // simt.cu
 
+int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                      int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, void* out, long long ldo,
+                      cudaStream_t stream);   // attn_fa.cu: ping-pong kernel for the long self-attention layers
+
 static constexpr int ATT_THREADS = 192;
 static constexpr int SLAB = 128 * 128;   // bytes of one [128 rows x 64 bf16] swizzled slab
 
@@ -290,6 +294,10 @@ extern "C" int b200ad_attention(int op_dtype, const void* q, long long ldq, cons
   B200AD_REQUIRE(op_dtype == 0, "attention: unknown op_dtype %d", op_dtype);
   B200AD_REQUIRE(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0, "attention: leading dims must be multiples of 8");
   B200AD_REQUIRE((d * 2) % 4 == 0 && (ldo % 2) == 0, "attention: output alignment");
+  {
+    const int rc = attention_bf16_fa(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out_op, ldo, st);
+    if (rc <= 0) return rc;          // served (0) or failed (<0); 1 = not a shape of the ping-pong kernel
+  }
   if (dpad == 64) return launch_attn_tc<64>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
   if (dpad == 128) return launch_attn_tc<128>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
   if (dpad == 192) return launch_attn_tc<192>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
