@@ -2,11 +2,13 @@
 // 9216 / 2304 at 768^2; head width 40 or 80).
 //   O = softmax(Q K^T / sqrt(d)) V per (frame-image n, head); bf16 operands, fp32 S / O accumulators in TMEM.
 // One CTA owns TWO query tiles of 128 rows (A and B) of one (n, head) and walks the keys in tiles of BN:
-//   warp 0      TMA producer: Q_A, Q_B once, then K_j / V_j through a ring of NST stages
-//   warp 1      UMMA issuer:  S_A(j)=Q_A K_j^T, S_B(j)=Q_B K_j^T, O_A+=P_A(j)V_j, O_B+=P_B(j)V_j, ordered so that the
-//               tensor pipe works on tile B while the softmax threads of tile A are busy, and vice versa
-//   warps 2..5  softmax of tile A, warps 6..9 softmax of tile B: one thread per query row; the whole score row is
+//   warps 0..3  softmax of tile A, warps 4..7 softmax of tile B: one thread per query row; the whole score row is
 //               held in registers (tcgen05.ld), exp2 with the running maximum, bf16 P written to swizzled smem
+//   warp 8      TMA producer: Q_A, Q_B once, then K_j / V_j through a ring of NST stages
+//   warp 9      UMMA issuer:  S_A(j)=Q_A K_j^T, S_B(j)=Q_B K_j^T, O_A+=P_A(j)V_j, O_B+=P_B(j)V_j; S_t(j+1) is issued as
+//               soon as the softmax threads of tile t hold S_t(j) in registers
+//   warps 10,11 idle (they complete the third warpgroup so that setmaxnreg can move registers: the softmax
+//               warpgroups run with 232 registers per thread, the third one with 40)
 // The layers this kernel serves are bound by the exponential (128 x 128 exp2 per 2.6 MFLOP of useful MMA at d=40),
 // so the structure aims at keeping both softmax groups busy all the time:
 //   * the O accumulator is rescaled lazily -- only when a row maximum grew by more than 2^8 since the last
@@ -17,7 +19,7 @@
 
 namespace b200ad {
 
-static constexpr int FA_THREADS = 320;
+static constexpr int FA_THREADS = 384;
 
 struct FaParams {
   int Lq, Lk, d, nkv;
@@ -29,9 +31,25 @@ struct FaParams {
 
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;
-  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+
+// 2^x on the FMA/ALU pipes (Cody-Waite split + degree-3 polynomial, FlashAttention-4's coefficients; relative error
+// ~1e-4, far below the bf16 rounding of P).  Valid for x in [-126, 126]; callers clamp below.
+__device__ __forceinline__ float poly_exp2(float x) {
+  x = fmaxf(x, -126.0f);
+  float j;
+  asm("add.rm.ftz.f32 %0, %1, %2;" : "=f"(j) : "f"(x), "f"(12582912.0f));   // 1.5 * 2^23: integer part in the mantissa
+  const float f = x - (j - 12582912.0f);                                     // fractional part in [0, 1)
+  float r = fmaf(0.077119089f, f, 0.227564f);
+  r = fmaf(r, f, 0.695146f);
+  r = fmaf(r, f, 1.0f);
+  return __int_as_float(__float_as_int(r) + (__float_as_int(j) << 23));
+}
+#ifndef B200AD_FA_EMU_EVERY
+#define B200AD_FA_EMU_EVERY 8      // every 8th exponential runs on the FMA pipes instead of the MUFU unit
+#endif
 
 // DP: padded head width (64 or 128).  BN: keys per tile (128 for DP=64, 64 for DP=128).
 template <int DP, int BN>
@@ -60,22 +78,28 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   uint64_t* s_full = kv_empty + NST;                   // [2]
   uint64_t* p_full = s_full + 2;                       // [2]  128 arrivals
   uint64_t* o_full = p_full + 2;                       // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+  uint64_t* s_read = o_full + 2;                       // [2]  128 arrivals: the S tile is in registers
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_read + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int qt = blockIdx.x, hd = blockIdx.y, n = blockIdx.z;     // qt: pair of 128-row query tiles
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     mbar_init(q_full, 1);
     for (int s = 0; s < NST; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&s_full[s], 1); mbar_init(&p_full[s], 128); mbar_init(&o_full[s], 1); }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&s_full[s], 1);
+      mbar_init(&p_full[s], 128);
+      mbar_init(&o_full[s], 1);
+      mbar_init(&s_read[s], 128);
+    }
     fence_barrier_init();
   }
-  if (warp == 1) {
+  if (warp == 9) {
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
   }
@@ -84,7 +108,9 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0) {
+  if (warp >= 8) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+  if (warp == 8) {
     // ===================== TMA producer (whole warp loops; one elected lane issues) =====================
     if (elect_one()) {
       mbar_arrive_expect_tx(q_full, 2 * NS * QSLAB);
@@ -110,7 +136,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       __syncwarp();
       if (++st == NST) { st = 0; ph ^= 1; }
     }
-  } else if (warp == 1) {
+  } else if (warp == 9) {
     // ===================== UMMA issuer =====================
     const uint32_t idesc_s = umma_idesc((uint32_t)BN, false, 1u);
     const uint32_t idesc_o = umma_idesc((uint32_t)DP, true, 1u);
@@ -153,23 +179,31 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       uint32_t ph_n = ph;
       if (st_n == NST) { st_n = 0; ph_n ^= 1; }
       const bool more = (j + 1 < p.nkv);
-      if (more) mbar_wait(&kv_full[st_n], ph_n);
-      // tile A: P_A(j) is in smem (and S_A has been read) -> O_A += P_A V_j, then S_A(j+1)
+      if (more) {
+        // S_t(j+1) as soon as the softmax threads of tile t hold S_t(j) in registers: the next score tile is
+        // ready before they finish their exponentials
+        mbar_wait(&kv_full[st_n], ph_n);
+        mbar_wait(&s_read[0], j & 1);
+        tc_fence_after();
+        issue_s(0, st_n);
+        mbar_wait(&s_read[1], j & 1);
+        tc_fence_after();
+        issue_s(1, st_n);
+      }
       mbar_wait(&p_full[0], j & 1);
       tc_fence_after();
       issue_pv(0, st, j == 0, false);
-      if (more) issue_s(0, st_n);
-      // tile B
       mbar_wait(&p_full[1], j & 1);
       tc_fence_after();
       issue_pv(1, st, j == 0, true);
-      if (more) issue_s(1, st_n);
       st = st_n;
       ph = ph_n;
     }
+  }
   } else {
-    // ===================== softmax: warps 2..5 -> tile A, warps 6..9 -> tile B; one thread per query row ====
-    const int t = (warp - 2) >> 2;
+    // ===================== softmax: warps 0..3 -> tile A, warps 4..7 -> tile B; one thread per query row ====
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    const int t = warp >> 2;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
@@ -187,26 +221,36 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 #pragma unroll
       for (int c = 0; c < BN; c += 32) tmem_ld_32x32b_x32(s_tmem + c, reinterpret_cast<uint32_t*>(s + c));
       tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(&s_read[t]);
       const int kbase = j * BN;
       if (kbase + BN > p.Lk) {
 #pragma unroll
         for (int i = 0; i < BN; ++i)
           if (kbase + i >= p.Lk) s[i] = -INFINITY;
       }
-      float mx = s[0];
+      // 8 independent chains: a single max / sum chain is 128 dependent 4-cycle ops per row
+      float mx8[8];
 #pragma unroll
-      for (int i = 1; i < BN; ++i) mx = fmaxf(mx, s[i]);
+      for (int i = 0; i < 8; ++i) mx8[i] = s[i];
+#pragma unroll
+      for (int i = 8; i < BN; ++i) mx8[i & 7] = fmaxf(mx8[i & 7], s[i]);
+      float mx = fmaxf(fmaxf(fmaxf(mx8[0], mx8[1]), fmaxf(mx8[2], mx8[3])),
+                       fmaxf(fmaxf(mx8[4], mx8[5]), fmaxf(mx8[6], mx8[7])));
       mx *= sc;
       // lazy rescale: keep the old reference maximum unless this row's maximum grew by more than 2^8
       const bool need = mx > m_used + 8.0f;
       const float m_new = need ? mx : m_used;
       const float neg_m = -m_new;
-      float sum = 0.f;
+      float sum8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int i = 0; i < BN; ++i) {
-        s[i] = fast_exp2(fmaf(s[i], sc, neg_m));
-        sum += s[i];
+        const float x = fmaf(s[i], sc, neg_m);
+        s[i] = (B200AD_FA_EMU_EVERY > 0 && (i % B200AD_FA_EMU_EVERY) == B200AD_FA_EMU_EVERY - 1) ? poly_exp2(x)
+                                                                                             : fast_exp2(x);
+        sum8[i & 7] += s[i];
       }
+      const float sum = ((sum8[0] + sum8[1]) + (sum8[2] + sum8[3])) + ((sum8[4] + sum8[5]) + (sum8[6] + sum8[7]));
       // PV(j-1) must be complete before P is overwritten or O rescaled
       if (j > 0) {
         mbar_wait(&o_full[t], (j - 1) & 1);
@@ -266,7 +310,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == 9) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
   }
@@ -297,7 +341,7 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)d);
   p.out = reinterpret_cast<bf16*>(out);
   p.ldo = ldo;
-  const size_t smem = (size_t)(2 * NS * 128 * 128 + 2 * 3 * NS * BN * 128 + 2 * (BN / 64) * 128 * 128) + 1024 + 256;
+  const size_t smem = (size_t)(2 * NS * 128 * 128 + 2 * 3 * NS * BN * 128 + 2 * (BN / 64) * 128 * 128) + 1024 + 256;  // slabs + alignment + barriers
   static bool attr = false;
   if (!attr) {
     B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
