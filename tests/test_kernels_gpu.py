@@ -246,21 +246,22 @@ def test_small_ops():
 
 
 @pytest.mark.parametrize("mode,tol", MODES)
-def test_conv_in_out(mode, tol):
+@pytest.mark.parametrize("B,Fr,h,w", [(2, 3, 16, 12), (1, 2, 5, 7), (2, 16, 32, 32)])
+def test_conv_in_out(mode, tol, B, Fr, h, w):
     o = ops(mode)
-    B, Fr, h, w = 2, 3, 16, 12
     s = rnd(B, 4, Fr, h, w, seed=1)
     wi, bi = rnd(320, 4, 3, 3, seed=2, scale=0.2), rnd(320, seed=3)
     x = s.permute(0, 2, 1, 3, 4).reshape(B * Fr, 4, h, w)
     ref = F.conv2d(x, wi, bi, padding=1).permute(0, 2, 3, 1).reshape(B * Fr * h * w, 320)
     out = o.conv_in(s.to(DEV), wi.to(DEV), bi.to(DEV))
-    assert rel(out.cpu(), ref) < 1e-5
+    assert rel(out.cpu(), ref) < 1e-5                                     # conv_in is fp32 SIMT in both modes
     act = bf(rnd(B * Fr, h, w, 320, seed=4))
-    wo, bo = rnd(4, 320, 3, 3, seed=5, scale=0.02), rnd(4, seed=6)
+    # bf16 mode: conv_out runs on warp-level MMAs with bf16 operands -> identical (bf16-representable) weights
+    wo, bo = bf(rnd(4, 320, 3, 3, seed=5, scale=0.02)), rnd(4, seed=6)
     y = F.conv2d(act.permute(0, 3, 1, 2), wo, bo, padding=1)             # [B*F, 4, h, w]
     ref = y.view(B, Fr, 4, h, w).permute(0, 2, 1, 3, 4)
     out = o.conv_out(act.to(DEV, o.op_dtype).view(-1, 320), B, Fr, h, w, wo.to(DEV), bo.to(DEV))
-    assert rel(out.cpu(), ref) < 1e-5
+    assert rel(out.cpu(), ref) < 1e-5                                     # exact products, fp32 accumulation
 
 
 def test_cfg_step_matches_formula():

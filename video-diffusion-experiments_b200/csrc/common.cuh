@@ -62,6 +62,22 @@ __device__ __forceinline__ float gelu_erf_f(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
 }
 
+// GELU(erf) for the bf16 GEMM epilogue: Abramowitz-Stegun 7.1.26 on z = |x|/sqrt(2),
+// erfc(z) = (a1 t + .. + a5 t^5) exp(-z^2), t = 1/(1 + p z); 12 FMA-pipe + 2 MUFU instructions instead of erff's ~30.
+// |gelu_fast - gelu_erf| <= 4.3e-7 absolute over [-12, 12] (< 0.09 bf16 ulp of the result wherever |result| > 1e-3).
+__device__ __forceinline__ float gelu_fast_f(float x) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  float t, e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -1.4426950408889634f));
+  float p = fmaf(1.061405429f, t, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  const float half_erfc = 0.5f * (p * t) * e;
+  return x * (x >= 0.f ? 1.0f - half_erfc : half_erfc);
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);

@@ -127,6 +127,114 @@ __global__ void gn_apply_kernel(const float* __restrict__ x0, int c0, const floa
   }
 }
 
+// ---- vectorised variants (C % 4 == 0, c0 % 4 == 0): one float4 (4 channels) per thread and row, R rows of the
+// block in flight side by side (thread = (row lane r, vector v)), 8 rows unrolled per thread => 128 bytes of loads
+// in flight per thread.  The float2 kernels above were latency-bound at 2.4-3.2 TB/s (32 B in flight per thread,
+// profiles/ncu_full_r01f.md: 29 % DRAM utilisation at 52 % occupancy).
+__device__ __forceinline__ float4 gn_load_vec(const float* x0, int c0, const float* x1, int c1, long long row, int c) {
+  return (c < c0) ? __ldcs(reinterpret_cast<const float4*>(x0 + row * c0 + c))
+                  : __ldcs(reinterpret_cast<const float4*>(x1 + row * c1 + (c - c0)));
+}
+static constexpr int GN_UNROLL = 8;
+
+__global__ void gn_stats_vec_kernel(const float* __restrict__ x0, int c0, const float* __restrict__ x1, int c1, int hw,
+                                    int groups, int R, float2* __restrict__ partial) {
+  extern __shared__ float2 sh[];          // [R][C]
+  const int C = c0 + c1;
+  const int nvec = C >> 2;
+  const int cpg = C / groups;
+  const int n = blockIdx.y, blk = blockIdx.x;
+  const int r0 = blk * GN_ROWS_PER_BLOCK;
+  const int r1 = min(hw, r0 + GN_ROWS_PER_BLOCK);
+  const int v = threadIdx.x % nvec, rl = threadIdx.x / nvec;
+  const int c = v * 4;
+  const float* base = (c < c0) ? x0 + c : x1 + (c - c0);
+  const long long ld = (c < c0) ? c0 : c1;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int r = r0 + rl; r < r1; r += R * GN_UNROLL) {
+    float4 t[GN_UNROLL];
+#pragma unroll
+    for (int u = 0; u < GN_UNROLL; ++u) {
+      const int rr = r + u * R;
+      t[u] = rr < r1 ? __ldg(reinterpret_cast<const float4*>(base + ((long long)n * hw + rr) * ld))
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < GN_UNROLL; ++u) {
+      s.x += t[u].x; s.y += t[u].y; s.z += t[u].z; s.w += t[u].w;
+      q.x += t[u].x * t[u].x; q.y += t[u].y * t[u].y; q.z += t[u].z * t[u].z; q.w += t[u].w * t[u].w;
+    }
+  }
+  float2* row = sh + (size_t)rl * C + c;
+  row[0] = make_float2(s.x, q.x); row[1] = make_float2(s.y, q.y);
+  row[2] = make_float2(s.z, q.z); row[3] = make_float2(s.w, q.w);
+  __syncthreads();
+  if (threadIdx.x < groups) {
+    const int g = threadIdx.x;
+    float ss = 0.f, qq = 0.f;
+    for (int rr = 0; rr < R; ++rr)
+      for (int cc = g * cpg; cc < (g + 1) * cpg; ++cc) { const float2 e = sh[(size_t)rr * C + cc]; ss += e.x; qq += e.y; }
+    partial[((long long)n * gridDim.x + blk) * groups + g] = make_float2(ss, qq);
+  }
+}
+
+template <typename T>
+__global__ void gn_apply_vec_kernel(const float* __restrict__ x0, int c0, const float* __restrict__ x1, int c1, int hw,
+                                    int groups, int R, const float2* __restrict__ meanrstd, int frames_per_stat,
+                                    const float* __restrict__ gamma, const float* __restrict__ beta, int silu,
+                                    T* __restrict__ out, T* __restrict__ raw) {
+  const int C = c0 + c1;
+  const int nvec = C >> 2;
+  const int cpg = C / groups;
+  const int n = blockIdx.y, blk = blockIdx.x;
+  const int r0 = blk * GN_ROWS_PER_BLOCK;
+  const int r1 = min(hw, r0 + GN_ROWS_PER_BLOCK);
+  const int v = threadIdx.x % nvec, rl = threadIdx.x / nvec;
+  const int c = v * 4;
+  const float2* mr = meanrstd + (n / frames_per_stat) * groups;
+  float sc[4], sf[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 m = mr[(c + j) / cpg];
+    sc[j] = gamma[c + j] * m.y;
+    sf[j] = beta[c + j] - m.x * sc[j];
+  }
+  const float* base = (c < c0) ? x0 + c : x1 + (c - c0);
+  const long long ld = (c < c0) ? c0 : c1;
+  for (int r = r0 + rl; r < r1; r += R * GN_UNROLL) {
+    float4 t[GN_UNROLL];
+#pragma unroll
+    for (int u = 0; u < GN_UNROLL; ++u) {
+      const int rr = r + u * R;
+      if (rr < r1) t[u] = __ldcs(reinterpret_cast<const float4*>(base + ((long long)n * hw + rr) * ld));
+    }
+#pragma unroll
+    for (int u = 0; u < GN_UNROLL; ++u) {
+      const int rr = r + u * R;
+      if (rr >= r1) break;
+      const long long o = ((long long)n * hw + rr) * C + c;
+      float4 y = make_float4(fmaf(t[u].x, sc[0], sf[0]), fmaf(t[u].y, sc[1], sf[1]), fmaf(t[u].z, sc[2], sf[2]),
+                             fmaf(t[u].w, sc[3], sf[3]));
+      if (silu) {
+        y.x = __fdividef(y.x, 1.0f + __expf(-y.x)); y.y = __fdividef(y.y, 1.0f + __expf(-y.y));
+        y.z = __fdividef(y.z, 1.0f + __expf(-y.z)); y.w = __fdividef(y.w, 1.0f + __expf(-y.w));
+      }
+      store4<T>(out + o, y);
+      if (raw) store4<T>(raw + o, t[u]);
+    }
+  }
+}
+
+// rows of a block processed side by side by the vectorised kernels (block = R * C/4 threads, ~256..640)
+static int gn_vec_R(int C) {
+  const int nvec = C / 4;
+  int R = (288 + nvec / 2) / nvec;
+  if (R < 1) R = 1;
+  if (R > 4) R = 4;
+  return R;
+}
+static bool gn_vec_ok(int C, int c0, int groups) { return C % 4 == 0 && c0 % 4 == 0 && C / 4 <= 1024 && C >= 128; }
+
 static int gn_threads(int C) {
   const int npairs = C / 2;
   int t = (npairs + GN_MAX_PPT - 1) / GN_MAX_PPT;
@@ -149,8 +257,13 @@ extern "C" int b200ad_gn_stats(const float* x0, int c0, const float* x1, int c1,
                  "gn_stats: unsupported channels C=%d (c0=%d) groups=%d", C, c0, groups);
   B200AD_REQUIRE(C / 2 <= 1024 * GN_MAX_PPT, "gn_stats: C=%d too large", C);
   dim3 grid(gn_nblk(hw), nimg);
-  gn_stats_kernel<<<grid, gn_threads(C), (C / 2) * sizeof(float2), (cudaStream_t)stream>>>(
-      x0, c0, x1, c1, hw, groups, reinterpret_cast<float2*>(partial));
+  if (gn_vec_ok(C, c0, groups)) {
+    const int R = gn_vec_R(C);
+    gn_stats_vec_kernel<<<grid, R * (C / 4), (size_t)R * C * sizeof(float2), (cudaStream_t)stream>>>(
+        x0, c0, x1, c1, hw, groups, R, reinterpret_cast<float2*>(partial));
+  } else
+    gn_stats_kernel<<<grid, gn_threads(C), (C / 2) * sizeof(float2), (cudaStream_t)stream>>>(
+        x0, c0, x1, c1, hw, groups, reinterpret_cast<float2*>(partial));
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -178,7 +291,15 @@ extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const floa
         part, nblk, frames_per_stat, groups, hw, C / groups, eps, meanrstd, nstat);
     count_launch();
   }
-  if (op_dtype == 0)
+  if (gn_vec_ok(C, c0, groups)) {
+    const int R = gn_vec_R(C);
+    if (op_dtype == 0)
+      gn_apply_vec_kernel<bf16><<<grid, R * (C / 4), 0, (cudaStream_t)stream>>>(
+          x0, c0, x1, c1, hw, groups, R, meanrstd, frames_per_stat, gamma, beta, silu, (bf16*)out_op, (bf16*)raw_op);
+    else
+      gn_apply_vec_kernel<float><<<grid, R * (C / 4), 0, (cudaStream_t)stream>>>(
+          x0, c0, x1, c1, hw, groups, R, meanrstd, frames_per_stat, gamma, beta, silu, (float*)out_op, (float*)raw_op);
+  } else if (op_dtype == 0)
     gn_apply_kernel<bf16><<<grid, gn_threads(C), 0, (cudaStream_t)stream>>>(
         x0, c0, x1, c1, hw, groups, meanrstd, frames_per_stat, gamma, beta, silu, (bf16*)out_op, (bf16*)raw_op);
   else

@@ -96,6 +96,60 @@ __global__ void conv_in_kernel(const float* __restrict__ sample, int B, int cin,
   }
 }
 
+// conv_in, compile-time cin (the UNet's cin = 4): KK = cin*9 weights per output channel live in registers, the
+// input patch of PIX pixels is staged once in smem as KK/4 float4 per pixel and read with broadcast LDS.128, so the
+// inner loop is 1 LDS.128 per 4 FFMA (FMA-bound, ~1.5 GFMA at 16f 512^2) and every store is a coalesced 4-byte
+// lane-contiguous write of the NHWC row.
+template <int CIN, int PIX>
+__global__ void __launch_bounds__(320) conv_in_fast_kernel(const float* __restrict__ sample, int B, int F, int h,
+                                                           int w, const float* __restrict__ W,
+                                                           const float* __restrict__ bias, int cout,
+                                                           float* __restrict__ out) {
+  constexpr int KK = CIN * 9;
+  static_assert(KK % 4 == 0, "patch rows are read as float4");
+  __shared__ __align__(16) float patch[PIX][KK];
+  const long long pix0 = (long long)blockIdx.x * PIX;
+  const long long npix = (long long)B * F * h * w;
+  for (int i = threadIdx.x; i < PIX * KK; i += blockDim.x) {
+    const int p = i / KK, k = i % KK;
+    const long long pix = pix0 + p;
+    float v = 0.f;
+    if (pix < npix) {
+      const int x = (int)(pix % w), y = (int)((pix / w) % h);
+      const int n = (int)(pix / ((long long)w * h));
+      const int b = n / F, f = n % F;
+      const int c = k / 9, ky = (k % 9) / 3, kx = k % 3;
+      const int yy = y + ky - 1, xx = x + kx - 1;
+      if (yy >= 0 && yy < h && xx >= 0 && xx < w)
+        v = sample[((((long long)b * CIN + c) * F + f) * h + yy) * w + xx];
+    }
+    patch[p][k] = v;
+  }
+  __syncthreads();
+  const int npx = (int)((npix - pix0) < PIX ? (npix - pix0) : PIX);
+  for (int co = threadIdx.x; co < cout; co += blockDim.x) {
+    float wreg[KK];
+#pragma unroll
+    for (int k = 0; k < KK; ++k) wreg[k] = W[(long long)co * KK + k];
+    const float bv = bias ? bias[co] : 0.f;
+    float* o = out + pix0 * cout + co;
+#pragma unroll 2
+    for (int p = 0; p < npx; ++p) {
+      const float4* pr = reinterpret_cast<const float4*>(patch[p]);
+      float a0 = bv, a1 = 0.f;
+#pragma unroll
+      for (int q = 0; q < KK / 4; ++q) {
+        const float4 v = pr[q];
+        a0 = fmaf(wreg[4 * q], v.x, a0);
+        a1 = fmaf(wreg[4 * q + 1], v.y, a1);
+        a0 = fmaf(wreg[4 * q + 2], v.z, a0);
+        a1 = fmaf(wreg[4 * q + 3], v.w, a1);
+      }
+      o[(long long)p * cout] = a0 + a1;
+    }
+  }
+}
+
 // conv_out: 3x3, pad 1, tiny cout (<= 4).  One warp per output pixel; lanes split the channel axis.
 template <typename T>
 __global__ void conv_out_kernel(const T* __restrict__ act, int B, int F, int h, int w, int cin,
@@ -135,6 +189,93 @@ __global__ void conv_out_kernel(const T* __restrict__ act, int B, int F, int h, 
     if (co < cout) {
       const float v = warp_sum(acc[co]);
       if (lane == 0) out[((((long long)b * cout + co) * F + f) * h + y) * w + x] = v + (bias ? bias[co] : 0.f);
+    }
+  }
+}
+
+// conv_out on warp-level tensor-core MMAs (bf16 operand mode): the 3x3 conv with cout <= 4 is the implicit GEMM
+// [pixels, 9*cin] x [9*cin, 8] (couts 4..7 are zero columns).  One warp owns 16 consecutive output pixels; per filter
+// tap and 32-channel block each lane fetches 16 bytes of two pixel rows (rows g and g+8 of the m16 tile) straight
+// from the NHWC activations and feeds them to two m16n8k16 MMAs -- the K order inside a block is permuted so that
+// one 16-byte load is the A fragment of both (lane q holds channels q*8..q*8+7: MMA s takes {4s,4s+1 | 4s+2,4s+3});
+// the weights are staged once per (persistent) block in smem in exactly that order, rows padded against bank
+// conflicts.  HBM-bound by construction: reads the activations once (taps hit L1/L2), writes [B,cout,F,h,w] fp32.
+// weight-row length in bf16 elements: rows 16 words apart (mod 32 banks), so the 8 lanes of an LDS.128 phase
+// (two rows x four 16-byte columns) cover all 32 banks once
+__host__ __device__ __forceinline__ int conv_out_wrow(int cin) { return cin + (((cin / 2) % 32 == 16) ? 0 : 32); }
+__device__ __forceinline__ void mma_bf16_m16n8k16(float* c, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                                  uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__global__ void __launch_bounds__(256) conv_out_mma_kernel(const bf16* __restrict__ act, int B, int F, int h, int w,
+                                                           int cin, const float* __restrict__ W,
+                                                           const float* __restrict__ bias, int cout,
+                                                           float* __restrict__ out) {
+  extern __shared__ __align__(16) uint8_t cosm[];
+  bf16* wsm = reinterpret_cast<bf16*>(cosm);              // [9][8][wrow]
+  const int wrow = conv_out_wrow(cin);
+  for (int i = threadIdx.x; i < 9 * 8 * cin; i += blockDim.x) {
+    const int c = i % cin, n = (i / cin) % 8, t = i / (8 * cin);
+    const float v = n < cout ? W[((long long)n * cin + c) * 9 + t] : 0.f;
+    wsm[(t * 8 + n) * wrow + c] = __float2bfloat16(v);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, q = lane & 3;
+  const long long npix = (long long)B * F * h * w;
+  const long long ngroups = (npix + 15) / 16;
+  const long long gstride = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long grp = (long long)blockIdx.x * (blockDim.x >> 5) + warp; grp < ngroups; grp += gstride) {
+    long long pix[2];
+    int px[2], py[2];
+    long long pn[2];
+    bool pv[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      pix[r] = grp * 16 + g + 8 * r;
+      pv[r] = pix[r] < npix;
+      const long long pp = pv[r] ? pix[r] : 0;
+      px[r] = (int)(pp % w);
+      py[r] = (int)((pp / w) % h);
+      pn[r] = pp / ((long long)w * h);
+    }
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 1
+    for (int t = 0; t < 9; ++t) {
+      const int dy = t / 3 - 1, dx = t % 3 - 1;
+      const bf16* ar[2];
+      bool ok[2];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int yy = py[r] + dy, xx = px[r] + dx;
+        ok[r] = pv[r] && yy >= 0 && yy < h && xx >= 0 && xx < w;
+        ar[r] = act + ((pn[r] * h + (ok[r] ? yy : 0)) * w + (ok[r] ? xx : 0)) * cin + q * 8;
+      }
+      const bf16* wr = wsm + (t * 8 + g) * wrow + q * 8;
+#pragma unroll 2
+      for (int c0 = 0; c0 < cin; c0 += 32) {
+        uint4 a_lo = make_uint4(0u, 0u, 0u, 0u), a_hi = make_uint4(0u, 0u, 0u, 0u);
+        if (ok[0]) a_lo = *reinterpret_cast<const uint4*>(ar[0] + c0);
+        if (ok[1]) a_hi = *reinterpret_cast<const uint4*>(ar[1] + c0);
+        const uint4 bw = *reinterpret_cast<const uint4*>(wr + c0);
+        mma_bf16_m16n8k16(acc, a_lo.x, a_hi.x, a_lo.y, a_hi.y, bw.x, bw.y);
+        mma_bf16_m16n8k16(acc, a_lo.z, a_hi.z, a_lo.w, a_hi.w, bw.z, bw.w);
+      }
+    }
+    // acc[0..1] = row g, couts 2q, 2q+1; acc[2..3] = row g+8
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      if (!pv[r]) continue;
+      const int b = (int)(pn[r] / F), f = (int)(pn[r] % F);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int co = 2 * q + j;
+        if (co < cout)
+          out[((((long long)b * cout + co) * F + f) * h + py[r]) * w + px[r]] = acc[2 * r + j] + (bias ? bias[co] : 0.f);
+      }
     }
   }
 }
@@ -194,8 +335,14 @@ extern "C" int b200ad_conv_in(const float* sample, int B, int cin, int F, int h,
   B200AD_REQUIRE(cin * 9 <= CIN_MAXK, "conv_in: cin=%d too large for the direct kernel", cin);
   const long long npix = (long long)B * F * h * w;
   const int threads = cout >= 320 ? 320 : ((cout + 31) / 32 * 32);
-  conv_in_kernel<<<(unsigned)((npix + CIN_PIX - 1) / CIN_PIX), threads, 0, (cudaStream_t)stream>>>(
-      sample, B, cin, F, h, w, W, bias, cout, out_nhwc);
+  if (cin == 4) {
+    constexpr int PIX = 32;
+    conv_in_fast_kernel<4, PIX><<<(unsigned)((npix + PIX - 1) / PIX), threads, 0, (cudaStream_t)stream>>>(
+        sample, B, F, h, w, W, bias, cout, out_nhwc);
+  } else {
+    conv_in_kernel<<<(unsigned)((npix + CIN_PIX - 1) / CIN_PIX), threads, 0, (cudaStream_t)stream>>>(
+        sample, B, cin, F, h, w, W, bias, cout, out_nhwc);
+  }
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -215,7 +362,22 @@ extern "C" int b200ad_conv_out(int op_dtype, const void* act_nhwc, int B, int F,
   const long long npix = (long long)B * F * h * w;
   const int threads = 512;     // 16 pixels per block amortise the weight staging
   const long long blocks = (npix * 32 + threads - 1) / threads;
-  if (op_dtype == 0)
+  if (op_dtype == 0 && cin % 32 == 0) {
+    static int sms = 0;
+    if (!sms) {
+      int dev = 0;
+      B200AD_CHECK_CUDA(cudaGetDevice(&dev));
+      B200AD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      B200AD_CHECK_CUDA(cudaFuncSetAttribute(conv_out_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+    }
+    const size_t wbytes = (size_t)9 * 8 * conv_out_wrow(cin) * sizeof(bf16);
+    B200AD_REQUIRE(wbytes <= 96 * 1024, "conv_out: weights need %zu bytes of shared memory", wbytes);
+    const long long ngroups = (npix + 15) / 16;
+    long long nb = (ngroups + 7) / 8;
+    if (nb > 2LL * sms) nb = 2LL * sms;
+    conv_out_mma_kernel<<<(unsigned)nb, 256, wbytes, (cudaStream_t)stream>>>((const bf16*)act_nhwc, B, F, h, w, cin, W,
+                                                                            bias, cout, out_bcfhw);
+  } else if (op_dtype == 0)
     conv_out_kernel<bf16><<<(unsigned)blocks, threads, smem, (cudaStream_t)stream>>>((const bf16*)act_nhwc, B, F, h, w, cin, W, bias, cout, out_bcfhw);
   else
     conv_out_kernel<float><<<(unsigned)blocks, threads, smem, (cudaStream_t)stream>>>((const float*)act_nhwc, B, F, h, w, cin, W, bias, cout, out_bcfhw);

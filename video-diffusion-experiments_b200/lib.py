@@ -11,7 +11,7 @@ import subprocess
 from ctypes import c_char_p, c_float, c_int, c_longlong, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200ad.so")
+LIB_PATH = os.environ.get("B200AD_LIB") or os.path.join(_HERE, "libb200ad.so")   # B200AD_LIB: profiling build
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
 _lib = None
