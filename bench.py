@@ -108,7 +108,7 @@ def cpu_reference_sample(n_samples: int, warmup: int, full_shape: bool):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     unet = make_oracle_unet(seed=0, round_to=None)
-    hw = 64 if full_shape else 32
+    hw = LAT_H if full_shape else 32
     g = torch.Generator().manual_seed(42)
     lat = torch.randn(1, 4, FRAMES, hw, hw, generator=g)
     txt = torch.randn(1, 77, 768, generator=torch.Generator().manual_seed(43))
@@ -285,9 +285,25 @@ def run_b200_arm(args):
         ms = sum(v["ms"] for v in tens.values())
         nl = sum(v["launches"] for v in tens.values())
         ach = fl / (ms * 1e-3) / 1e12
+        # DRAM traffic of the same kernel from the committed ncu launch list (profiles/traffic.json, written by
+        # tools/summarize_launches.py from `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum`): average
+        # bytes per launch, like `achieved`; null when no capture is committed
+        traffic, traffic_src = None, None
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                tj = json.load(f)
+            g = tj.get("gemm_tc_kernel")
+            if g and g.get("dram_bytes"):
+                traffic = g["dram_bytes"] / g["launches"]
+                traffic_src = f"profiles/traffic.json ({g['launches']} launches of one step under ncu)"
+        except Exception:
+            pass
+        alg_bytes = sum(v["bytes"] for v in tens.values()) / max(nl, 1)
         roof = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 GEMM + implicit-GEMM conv3x3)",
                 "achieved": ach, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
-                "frac": ach / pk["bf16_tflops_sustained"], "traffic": None, "peak_source": pk["source"] + " (sustained)",
+                "frac": ach / pk["bf16_tflops_sustained"], "traffic": traffic, "traffic_unit": "bytes per launch",
+                "traffic_source": traffic_src, "algorithmic_bytes_per_launch": alg_bytes,
+                "peak_source": pk["source"] + " (sustained)",
                 "launches_per_step": nl, "avg_launch_ms": ms / max(nl, 1),
                 "share_of_step": ms / sum(v["ms"] for v in fam.values()),
                 "how": "CUDA events around every launch of one eager step (no graph), algorithmic FLOPs 2MNK"}
@@ -330,6 +346,7 @@ def run_b200_arm(args):
 
 
 def main():
+    global FRAMES, LAT_H, LAT_W, NUM_STEPS, GUIDANCE, FLOPS_PER_STEP, WORKLOAD, METRIC
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=25)
@@ -337,7 +354,20 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    # other BASELINE configs (not the default bench line): --frames 32 --latent 96 = configs[4] (32f 768^2);
+    # --num-steps 15 --guidance 9.0 with --gpus 2 = configs[2]
+    ap.add_argument("--frames", type=int, default=FRAMES)
+    ap.add_argument("--latent", type=int, default=LAT_H)
+    ap.add_argument("--num-steps", type=int, default=NUM_STEPS)
+    ap.add_argument("--guidance", type=float, default=GUIDANCE)
     args = ap.parse_args()
+    if (args.frames, args.latent, args.num_steps, args.guidance) != (FRAMES, LAT_H, NUM_STEPS, GUIDANCE):
+        from tools.flops import unet_flops
+        FRAMES, LAT_H, LAT_W, NUM_STEPS, GUIDANCE = args.frames, args.latent, args.latent, args.num_steps, args.guidance
+        FLOPS_PER_STEP = unet_flops(2, FRAMES, LAT_H)["total"]
+        WORKLOAD = (f"AnimateDiff SD1.5 UNet + motion-adapter v1.5 (random init), {FRAMES} frames {8 * LAT_H}x{8 * LAT_W}, "
+                    f"{NUM_STEPS} DDIM steps, CFG {GUIDANCE}, bf16")
+        METRIC = f"denoise steps/s ({FRAMES}f {8 * LAT_H}^2)"
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_b200_arm(args)

@@ -70,6 +70,12 @@ int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const float* x1, int 
                     const float* partial, int frames_per_stat, float eps, const float* gamma, const float* beta,
                     int silu, void* out_op, void* raw_op, void* stream);
 
+/* Statistics + apply in one call (same arguments and workspace as the pair above), walked over sub-batches of
+ * images sized to the L2 so that the apply pass re-reads its input from L2 instead of HBM. */
+int b200ad_group_norm(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
+                      float* partial, int frames_per_stat, float eps, const float* gamma, const float* beta, int silu,
+                      void* out_op, void* raw_op, void* stream);
+
 /* ---- K7: LayerNorm (+ sinusoidal positional-embedding add of the motion module; replaces nn.LayerNorm and
  * SinusoidalPositionalEmbedding).  x fp32 [rows,C]; pe fp32 [max_seq,C] or NULL; frame index of a row is
  * (row / hw) % frames. */

@@ -126,7 +126,9 @@ def test_conv3x3_stride2_and_upsample(mode, tol, n, h, w, c):
 @pytest.mark.parametrize("mode,tol", MODES)
 @pytest.mark.parametrize("nimg,hw,c0,c1,fps,silu", [(4, 256, 320, 0, 1, True), (4, 64, 1280, 640, 1, True),
                                                     (8, 1024, 640, 320, 1, True), (8, 100, 320, 0, 4, False),
-                                                    (2, 4096, 64, 0, 2, False), (3, 16, 2560, 0, 1, True)])
+                                                    (2, 4096, 64, 0, 2, False), (3, 16, 2560, 0, 1, True),
+                                                    # > 72 MB of fp32 input: walked in L2-sized sub-batches
+                                                    (28, 1024, 640, 0, 1, True), (32, 1024, 320, 320, 16, False)])
 def test_group_norm(mode, tol, nimg, hw, c0, c1, fps, silu):
     o = ops(mode)
     x0 = rnd(nimg * hw, c0, seed=1) * 2 + 0.5

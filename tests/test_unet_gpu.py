@@ -36,7 +36,10 @@ SMALL = dict(block_out_channels=(64, 128, 256, 256))
 
 
 @pytest.mark.parametrize("mode", ["bf16", "fp32"])
-@pytest.mark.parametrize("B,F,h,w,t", [(2, 16, 16, 16, 925), (1, 8, 8, 24, 1), (2, 5, 16, 8, 500.5)])
+@pytest.mark.parametrize("B,F,h,w,t", [(2, 16, 16, 16, 925), (1, 8, 8, 24, 1), (2, 5, 16, 8, 500.5),
+                                       # BASELINE configs[4] geometry in small: 32 frames (the PE-table limit), latent
+                                       # sides 48/24/12/6 (768^2 gives 96/48/24/12: non-power-of-two token counts)
+                                       (1, 32, 48, 48, 961)])
 def test_small_unet_matches_oracle(mode, B, F, h, w, t):
     oracle, prod = _pair(SMALL)
     prod.set_mode(mode)

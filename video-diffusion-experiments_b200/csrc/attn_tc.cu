@@ -28,12 +28,15 @@ struct AttnParams {
   long long ldo;
 };
 
-template <int DP>
+// NST: K/V ring depth.  Text cross-attention (Lk = 77: one key tile) runs with NST = 1, which at DP = 64 brings the
+// CTA to 81 KB of shared memory so that TWO CTAs share an SM (TMEM: 2 x 256 columns): the kernel is a serial
+// load -> S -> softmax -> PV -> store chain per CTA, so residency is its only source of overlap (one CTA per SM
+// measured 9 % occupancy and 6 % of HBM bandwidth, profiles/ncu_full_r01f.md).
+template <int DP, int NST>
 __global__ void __launch_bounds__(ATT_THREADS, (DP == 64) ? 2 : 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ AttnParams p) {
   constexpr int NS = DP / 64;                  // 64-column slabs per operand tile
-  constexpr int NST = (DP <= 128) ? 2 : 1;     // K/V ring depth
   constexpr uint32_t TMEM_COLS = (128 + DP <= 256) ? 256u : 512u;
   constexpr uint32_t O_COL = 128;
 
@@ -237,12 +240,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   }
 }
 
-template <int DP>
+template <int DP, int NST>
 static int launch_attn_tc(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                           int nbatch, int heads, int Lq, int Lk, int d, int kv_div, void* out, long long ldo,
                           cudaStream_t stream) {
   constexpr int NS = DP / 64;
-  constexpr int NST = (DP <= 128) ? 2 : 1;
   CUtensorMap tmQ, tmK, tmV;
   const int nkvb = (nbatch + kv_div - 1) / kv_div;
   {
@@ -268,11 +270,11 @@ static int launch_attn_tc(const void* q, long long ldq, const void* k, long long
   const size_t smem = (size_t)(NS + 2 * NST * NS + 2) * SLAB + 1024 + 128;
   static bool attr = false;
   if (!attr) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel<DP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel<DP, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr = true;
   }
   dim3 grid((Lq + 127) / 128, heads, nbatch);
-  attn_tc_kernel<DP><<<grid, ATT_THREADS, smem, stream>>>(tmQ, tmK, tmV, p);
+  attn_tc_kernel<DP, NST><<<grid, ATT_THREADS, smem, stream>>>(tmQ, tmK, tmV, p);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -298,9 +300,15 @@ extern "C" int b200ad_attention(int op_dtype, const void* q, long long ldq, cons
     const int rc = attention_bf16_fa(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out_op, ldo, st);
     if (rc <= 0) return rc;          // served (0) or failed (<0); 1 = not a shape of the ping-pong kernel
   }
-  if (dpad == 64) return launch_attn_tc<64>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
-  if (dpad == 128) return launch_attn_tc<128>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
-  if (dpad == 192) return launch_attn_tc<192>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
+  const bool one_tile = Lk <= 128;
+  if (dpad == 64)
+    return one_tile ? launch_attn_tc<64, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st)
+                    : launch_attn_tc<64, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
+  if (dpad == 128)
+    return one_tile ? launch_attn_tc<128, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st)
+                    : launch_attn_tc<128, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
+  if (dpad == 192)
+    return launch_attn_tc<192, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
   set_error("attention: dpad=%d unsupported on the tcgen05 path (64, 128, 192)", dpad);
   return -1;
 }

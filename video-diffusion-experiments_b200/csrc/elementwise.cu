@@ -132,8 +132,8 @@ __global__ void gn_apply_kernel(const float* __restrict__ x0, int c0, const floa
 // in flight per thread.  The float2 kernels above were latency-bound at 2.4-3.2 TB/s (32 B in flight per thread,
 // profiles/ncu_full_r01f.md: 29 % DRAM utilisation at 52 % occupancy).
 __device__ __forceinline__ float4 gn_load_vec(const float* x0, int c0, const float* x1, int c1, long long row, int c) {
-  return (c < c0) ? __ldcs(reinterpret_cast<const float4*>(x0 + row * c0 + c))
-                  : __ldcs(reinterpret_cast<const float4*>(x1 + row * c1 + (c - c0)));
+  return (c < c0) ? __ldg(reinterpret_cast<const float4*>(x0 + row * c0 + c))
+                  : __ldg(reinterpret_cast<const float4*>(x1 + row * c1 + (c - c0)));
 }
 static constexpr int GN_UNROLL = 8;
 
@@ -206,7 +206,7 @@ __global__ void gn_apply_vec_kernel(const float* __restrict__ x0, int c0, const 
 #pragma unroll
     for (int u = 0; u < GN_UNROLL; ++u) {
       const int rr = r + u * R;
-      if (rr < r1) t[u] = __ldcs(reinterpret_cast<const float4*>(base + ((long long)n * hw + rr) * ld));
+      if (rr < r1) t[u] = __ldg(reinterpret_cast<const float4*>(base + ((long long)n * hw + rr) * ld));
     }
 #pragma unroll
     for (int u = 0; u < GN_UNROLL; ++u) {
@@ -307,5 +307,43 @@ extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const floa
         x0, c0, x1, c1, hw, groups, meanrstd, frames_per_stat, gamma, beta, silu, (float*)out_op, (float*)raw_op);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Fused GroupNorm: statistics + finalize + apply in one call, walked over sub-batches of images that fit the L2
+// (the apply pass of a sub-batch re-reads what its statistics pass just pulled into the 126 MB L2; with two whole-
+// tensor passes the 168-503 MB level-0 tensors were read from HBM twice).  Same workspace layout as gn_stats/gn_apply.
+extern "C" int b200ad_group_norm(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
+                                 int groups, float* partial, int frames_per_stat, float eps, const float* gamma,
+                                 const float* beta, int silu, void* out_op, void* raw_op, void* stream) {
+  if (!x1) c1 = 0;
+  const int C = c0 + c1;
+  B200AD_REQUIRE(frames_per_stat >= 1 && nimg % frames_per_stat == 0, "group_norm: nimg=%d frames_per_stat=%d", nimg,
+                 frames_per_stat);
+  const double img_bytes = (double)hw * C * 4.0;
+  const double budget = 56e6;                       // fp32 input bytes per sub-batch (its bf16 output shares the L2)
+  int chunk = nimg;
+  if (img_bytes * nimg > 72e6) {
+    chunk = (int)(budget / img_bytes);
+    if (chunk < frames_per_stat) chunk = frames_per_stat;
+    chunk -= chunk % frames_per_stat;
+    if (chunk > nimg) chunk = nimg;
+  }
+  const int nblk = gn_nblk(hw);
+  const size_t esz = op_dtype == 0 ? 2 : 4;
+  // per-call layout of `partial`: [nimg*nblk*groups] float2 partial sums, then [nimg*groups] float2 (mean, rstd);
+  // a sub-batch uses a prefix of each region
+  for (int n0 = 0; n0 < nimg; n0 += chunk) {
+    const int nn = (nimg - n0 < chunk) ? nimg - n0 : chunk;
+    const long long roff = (long long)n0 * hw;
+    const float* a0 = x0 + roff * c0;
+    const float* a1 = x1 ? x1 + roff * c1 : nullptr;
+    if (int rc = b200ad_gn_stats(a0, c0, a1, c1, nn, hw, groups, partial, stream)) return rc;
+    char* o = reinterpret_cast<char*>(out_op) + (size_t)roff * C * esz;
+    char* r = raw_op ? reinterpret_cast<char*>(raw_op) + (size_t)roff * C * esz : nullptr;
+    if (int rc = b200ad_gn_apply(op_dtype, a0, c0, a1, c1, nn, hw, groups, partial, frames_per_stat, eps, gamma, beta,
+                                 silu, o, r, stream))
+      return rc;
+  }
   return 0;
 }

@@ -78,7 +78,10 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t local_smem_addr, uint32_t 
   return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  // default semantics (.release at CTA scope): the accumulator hand-off is ordered by tcgen05.wait::ld +
+  // tcgen05.fence::before_thread_sync; a cluster-scope release compiles to MEMBAR + ERRBAR (~1000 cycles per tile
+  // and warp in profiles/ncu_full_r01f)
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA loads of a CTA pair: data lands in this CTA's smem, the transaction bytes are reported to the mbarrier at
 // cluster address `bar` (the leader CTA's full barrier).
@@ -162,8 +165,10 @@ __device__ __forceinline__ int tile_chunks(const TcParams& p, int n_tile) {
 
 // Iterator over the chunks one epilogue group processes: tiles blockIdx-strided, chunks c = g, g+2, ...
 // The tile's coordinates are cached so the integer divisions happen once per tile, not once per chunk.
+// Chunk c of the cluster's it-th tile belongs to epilogue group (c + it) & 1: with an odd number of chunks per tile
+// (BN = 160: five) the group that gets three of them alternates from tile to tile.
 struct ChunkCursor {
-  int tile, c, nchunks;
+  int tile, c, nchunks, it;
   TileCoord t;
 };
 __device__ __forceinline__ void cursor_load(const TcParams& p, ChunkCursor& cur, int num_tiles, int rank) {
@@ -176,7 +181,8 @@ __device__ __forceinline__ void cursor_settle(const TcParams& p, ChunkCursor& cu
                                               int rank) {
   while (cur.tile < num_tiles && cur.c >= cur.nchunks) {
     cur.tile += stride;
-    cur.c = g;
+    cur.it += 1;
+    cur.c = (g ^ cur.it) & 1;
     cursor_load(p, cur, num_tiles, rank);
   }
 }
@@ -235,6 +241,7 @@ __device__ __forceinline__ void io_group_init(const TcParams& p, const EpiMaps& 
   G.prev_buf = p.nbuf - 1;           // the one buffer not handed out below
   G.phase = 0;
   G.pre.tile = cluster_id;
+  G.pre.it = 0;
   G.pre.c = g;
   cursor_load(p, G.pre, num_tiles, rank);
   cursor_settle(p, G.pre, g, num_tiles, num_clusters, rank);
@@ -259,7 +266,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* res_full = tempty_bar + 2;                  // [2][MAX_NBUF] chunk buffer ready (per epilogue group)
   uint64_t* chunk_done = res_full + 2 * MAX_NBUF;       // [2][MAX_NBUF] chunk written to smem by its 128 threads
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(chunk_done + 2 * MAX_NBUF);
-  float* sbias = reinterpret_cast<float*>(smem + p.off_bias);   // [2][256]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -424,12 +430,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int last_g = -1;
     long long io_wait_done = 0, io_wait_read = 0, io_issue = 0;
     const long long io_begin = prof_clock();
-    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+    int io_it = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++io_it) {
       const TileCoord t = tile_coord(p, tile, rank);
       const int nchunks = tile_chunks(p, t.n_tile);
       const int ocol0 = (t.n_tile * p.BN) >> (p.geglu ? 1 : 0);
       for (int c = 0; c < nchunks; ++c) {
-        const int g = c & 1;
+        const int g = (c + io_it) & 1;
         IoGroup& G = g ? G1 : G0;
         const long long i0 = prof_clock();
         mbar_wait(&G.cdone[G.buf], G.phase);
@@ -452,11 +459,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           // the store of this group's previous chunk is the 2nd (or, at an odd tile boundary, the 1st) most recent
           if (last_g == g) tma_store_wait_read1(); else tma_store_wait_read2();
           io_wait_read += prof_clock() - i2;
-          if (G.pre.tile < num_tiles)
+          // no residual: the hand-off is a bare arrive, no look-ahead cursor to maintain (a surplus arrive after
+          // the group's last chunk completes a phase nobody waits for)
+          if (!p.has_res) mbar_arrive(&G.ready[G.prev_buf]);
+          else if (G.pre.tile < num_tiles)
             chunk_prefetch(p, em, G.f32 + (size_t)G.prev_buf * F32_BUF_BYTES, &G.ready[G.prev_buf], G.pre, rank);
         }
         __syncwarp();
-        if (G.pre.tile < num_tiles) {
+        if (p.has_res && G.pre.tile < num_tiles) {
           G.pre.c += 2;
           cursor_settle(p, G.pre, g, num_tiles, num_clusters, rank);
         }
@@ -494,44 +504,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int as = it & 1;
       const TileCoord t = tile_coord(p, tile, rank);
       const int nchunks = tile_chunks(p, t.n_tile);
-      // ---- bias (+ timestep-embedding row when it is the same for all rows of the tile) -> smem
+      // ---- bias / timestep-embedding row: read straight from global memory in the chunk loop (every thread of a
+      // warp reads the same 128 bytes of `bias`: one L1-resident broadcast line per chunk).  Staging them in smem
+      // cost a block-wide named barrier per tile, which showed up as ~5 % of the epilogue at K = 320.
       long long out_row = 0;
-      bool rb_uniform = true;
       if (p.row_bias) {
-        long long first, last;
         if (p.conv) {
-          first = (long long)t.n0 * p.h * p.w;
-          int nl = t.n0 + p.n_box - 1;
-          if (nl > p.nimg - 1) nl = p.nimg - 1;
-          last = ((long long)nl + 1) * p.h * p.w - 1;
           const int x = t.x0 + (r % p.w_box), y = t.y0 + ((r / p.w_box) % p.h_box);
           int n = t.n0 + r / (p.w_box * p.h_box);
           if (n > p.nimg - 1) n = p.nimg - 1;
           out_row = ((long long)n * p.h + (y < p.h ? y : p.h - 1)) * p.w + (x < p.w ? x : p.w - 1);
         } else {
-          first = (long long)t.m_tile * BM;
-          last = first + BM - 1;
-          if (last > p.M - 1) last = p.M - 1;
-          if (first > p.M - 1) first = p.M - 1;
-          out_row = first + r;
+          out_row = (long long)t.m_tile * BM + r;
           if (out_row > p.M - 1) out_row = p.M - 1;
         }
-        rb_uniform = (first / p.rb_div) == (last / p.rb_div);
       }
-      float* sb = sbias + (it & 1) * 256;
       const long long q0 = prof_clock();
-      if (et < p.BN) {
-        const int col = t.n_tile * p.BN + et;
-        float v = 0.f;
-        if (col < p.N) {
-          if (p.bias) v = p.bias[col];
-          if (p.row_bias && rb_uniform) v += p.row_bias[(out_row / p.rb_div) * (long long)p.ld_rb + col];
-        }
-        asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_u32(sb + et)), "f"(v) : "memory");
-      }
-      named_bar_sync(3, EPI_THREADS);
+      const float* bias_t = p.bias ? p.bias + t.n_tile * p.BN : nullptr;
       const float* rb_row =
-          (p.row_bias && !rb_uniform) ? p.row_bias + (out_row / p.rb_div) * (long long)p.ld_rb + t.n_tile * p.BN : nullptr;
+          p.row_bias ? p.row_bias + (out_row / p.rb_div) * (long long)p.ld_rb + t.n_tile * p.BN : nullptr;
 
       const long long q1 = prof_clock();
       e_bias += q1 - q0;
@@ -539,7 +530,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       e_tfull += prof_clock() - q1;
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * p.BN);
-      for (int c = g; c < nchunks; c += 2, ++k) {
+      for (int c = (g ^ it) & 1; c < nchunks; c += 2, ++k) {
         uint8_t* fb = f32bufs + (size_t)buf * F32_BUF_BYTES;
         uint8_t* ob = opbufs + (size_t)buf * OP_BUF_BYTES;
         float v[32];
@@ -547,14 +538,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           uint32_t acc[32];
           tmem_ld_32x32b_x32(taddr + (uint32_t)(c * AW), acc);
           tmem_wait_ld();
-          const uint32_t sb_a = smem_u32(sb) + (uint32_t)(c * AW * 4);
+          const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          const float4* bp = reinterpret_cast<const float4*>(bias_t + c * AW);
           if (p.geglu) {
             uint32_t acc2[32];
             tmem_ld_32x32b_x32(taddr + (uint32_t)(c * AW + 32), acc2);
             tmem_wait_ld();
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 b0 = lds_f4(sb_a + 16 * j), b1 = lds_f4(sb_a + 128 + 16 * j);
+              const float4 b0 = bias_t ? __ldg(bp + j) : z4, b1 = bias_t ? __ldg(bp + 8 + j) : z4;
               v[2 * j] = (__uint_as_float(acc[4 * j]) + b0.x) * gelu_fast_f(__uint_as_float(acc[4 * j + 1]) + b0.y);
               v[2 * j + 1] = (__uint_as_float(acc[4 * j + 2]) + b0.z) * gelu_fast_f(__uint_as_float(acc[4 * j + 3]) + b0.w);
               v[16 + 2 * j] = (__uint_as_float(acc2[4 * j]) + b1.x) * gelu_fast_f(__uint_as_float(acc2[4 * j + 1]) + b1.y);
@@ -564,7 +556,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           } else {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float4 b = lds_f4(sb_a + 16 * j);
+              const float4 b = bias_t ? __ldg(bp + j) : z4;
               v[4 * j] = __uint_as_float(acc[4 * j]) + b.x;
               v[4 * j + 1] = __uint_as_float(acc[4 * j + 1]) + b.y;
               v[4 * j + 2] = __uint_as_float(acc[4 * j + 2]) + b.z;
@@ -573,7 +565,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (rb_row) {
 #pragma unroll
               for (int j = 0; j < 32; j += 4) {
-                const float4 q = *reinterpret_cast<const float4*>(rb_row + c * 32 + j);
+                const float4 q = __ldg(reinterpret_cast<const float4*>(rb_row + c * 32 + j));
                 v[j] += q.x; v[j + 1] += q.y; v[j + 2] += q.z; v[j + 3] += q.w;
               }
             }
@@ -746,10 +738,30 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   const int fixed = 2 * 256 * 4 + 512;                       // bias staging + barriers
   const int budget = SMEM_LIMIT - 1024 - fixed;
   int want_stages = p.num_kb < 6 ? (p.num_kb < 3 ? 3 : p.num_kb) : 6;
+  {
+    // HBM-bound shapes (the small-K GEMMs over the fp32 residual stream) are paced by the epilogue's bytes in flight,
+    // not by the mainloop: give the shared memory to chunk buffers (residual prefetch depth nbuf-1) before stages.
+    // With 6 stages the K=320 res32 GEMMs were left with nbuf=2, i.e. ONE residual chunk prefetched per group
+    // (epilogue waiting on the residual 38 % of its time, tools/gemm_waits.py).
+    const double t_mma = 2.0 * a.M * (double)a.N * a.K / 1.4e15;
+    const double bytes = (double)a.M * a.K * 2 + (double)a.M * n_out * ((p.has_res ? 4 : 0) + (p.has_o32 ? 4 : 0) + (p.has_oop ? 2 : 0));
+    if (bytes / 6.5e12 > t_mma) {
+      // stages cover the A operand's share of the bytes in flight (~180 KB per SM at 2 us of loaded latency):
+      // 3 stages when A is 20 % of the traffic (K = 320 res32), 6 when it is half of it (K = 1280 res32: with 3
+      // stages the MMA warp waited for operands 64 % of the time).
+      const double a_frac = (double)a.M * a.K * 2 / bytes;
+      int st = (int)(11.0 * a_frac + 0.999);
+      if (st < 3) st = 3;
+      if (st < want_stages) want_stages = st;
+    }
+  }
   p.nbuf = MAX_NBUF;
   while (p.nbuf > 2 && want_stages * p.stage_bytes + 2 * p.nbuf * per_buf > budget) --p.nbuf;
   p.num_stages = (budget - 2 * p.nbuf * per_buf) / p.stage_bytes;
   if (p.num_stages > MAX_STAGES) p.num_stages = MAX_STAGES;
+  if (getenv("B200AD_GEMM_VERBOSE"))
+    fprintf(stderr, "gemm M=%d N=%d K=%d BN=%d stages=%d nbuf=%d res=%d o32=%d oop=%d geglu=%d\n", a.M, a.N, a.K, p.BN,
+            p.num_stages, p.nbuf, p.has_res, p.has_o32, p.has_oop, p.geglu);
   B200AD_REQUIRE(p.num_stages >= 2, "gemm: shared memory plan failed (BN=%d)", p.BN);
   p.off_f32 = p.num_stages * p.stage_bytes;
   p.off_op = p.off_f32 + ((p.has_res || p.has_o32) ? 2 * p.nbuf * F32_BUF_BYTES : 0);

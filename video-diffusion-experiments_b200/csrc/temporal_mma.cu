@@ -50,20 +50,34 @@ temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int
   const int C3 = 3 * C;
   const int cpp = W >> 3;                // 16-byte chunks per part per row
 
-  // ---- gather: PB positions x FP rows x (q|k|v) segments; rows >= F are zero (finite padding for the MMAs)
-  const int total = PB * FP * 3 * cpp;
-  for (int i = threadIdx.x; i < total; i += blockDim.x) {
-    const int ch = i % cpp;
-    const int part = (i / cpp) % 3;
-    const int f = (i / (3 * cpp)) % FP;
-    const int p = i / (3 * cpp * FP);
-    bf16* dst = sm + (size_t)(p * FP + f) * RS + part * W + ch * 8;
-    const int pos = pos0 + p;
-    if (f < F && pos < npos) {
-      const int b = pos / hw, s = pos - b * hw;
-      cp_async16(dst, qkv + ((long long)(b * F + f) * hw + s) * C3 + part * C + col0 + ch * 8);
-    } else {
-      *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+  // ---- gather: PB positions x FP rows x (q|k|v) segments; rows >= F are zero (finite padding for the MMAs).
+  // Index math is incremental (one division per thread, then adds and compares): with `i / cpp`, `% 3`, `/ hw`
+  // per 16-byte chunk the integer divisions were 60 % of the kernel's instructions and made it issue-bound
+  // (profiles/ncu_full_r01f.md: 118 M warp instructions, SM 75 % busy at 26 % DRAM utilisation).
+  __shared__ long long pos_base[8], out_base[8];
+  if (threadIdx.x < PB) {
+    const int pos = pos0 + threadIdx.x;
+    const int b = pos < npos ? pos / hw : 0, sp = pos < npos ? pos - b * hw : 0;
+    pos_base[threadIdx.x] = pos < npos ? ((long long)b * F * hw + sp) * C3 + col0 : -1;
+    out_base[threadIdx.x] = ((long long)b * F * hw + sp) * C + col0;
+  }
+  __syncthreads();
+  {
+    const int rowlen = 3 * cpp;                        // 16-byte chunks per smem row
+    const int nrows = PB * FP;
+    const int dcol = (int)blockDim.x % rowlen, drow = (int)blockDim.x / rowlen;
+    int row = (int)threadIdx.x / rowlen, col = (int)threadIdx.x - row * rowlen;
+    const long long fstride = (long long)hw * C3;
+    for (; row < nrows; ) {
+      const int part = (col >= cpp) + (col >= 2 * cpp);
+      const int ch = col - part * cpp;
+      const int f = row & (FP - 1), pp = row / FP;     // FP is a compile-time power of two
+      bf16* dst = sm + (size_t)row * RS + part * W + ch * 8;
+      const long long pb = pos_base[pp];
+      if (f < F && pb >= 0) cp_async16(dst, qkv + pb + f * fstride + part * C + ch * 8);
+      else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+      col += dcol; row += drow;
+      if (col >= rowlen) { col -= rowlen; ++row; }
     }
   }
   cp_async_wait_all();
@@ -183,17 +197,22 @@ temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int
     }
   }
   __syncthreads();
-  // ---- scatter: the q part of smem now holds O for all heads of the group
-  const int total_o = PB * F * cpp;
-  for (int i = threadIdx.x; i < total_o; i += blockDim.x) {
-    const int ch = i % cpp;
-    const int f = (i / cpp) % F;
-    const int pp = i / (cpp * F);
-    const int pos = pos0 + pp;
-    if (pos >= npos) continue;
-    const int b = pos / hw, s = pos - b * hw;
-    const uint4 v = *reinterpret_cast<const uint4*>(sm + (size_t)(pp * FP + f) * RS + ch * 8);
-    *reinterpret_cast<uint4*>(out + ((long long)(b * F + f) * hw + s) * C + col0 + ch * 8) = v;
+  // ---- scatter: the q part of smem now holds O for all heads of the group (same incremental indexing)
+  {
+    const int dcol = (int)blockDim.x % cpp, drow = (int)blockDim.x / cpp;
+    const long long fstride = (long long)hw * C;
+    for (int pp = 0; pp < PB; ++pp) {
+      const long long pb = pos_base[pp];
+      if (pb < 0) break;
+      const long long ob = out_base[pp];
+      int f = (int)threadIdx.x / cpp, ch = (int)threadIdx.x - f * cpp;
+      for (; f < F; ) {
+        const uint4 v = *reinterpret_cast<const uint4*>(sm + (size_t)(pp * FP + f) * RS + ch * 8);
+        *reinterpret_cast<uint4*>(out + ob + f * fstride + ch * 8) = v;
+        ch += dcol; f += drow;
+        if (ch >= cpp) { ch -= cpp; ++f; }
+      }
+    }
   }
 }
 

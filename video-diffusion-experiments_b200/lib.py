@@ -28,6 +28,7 @@ SIGNATURES = {
     "b200ad_gn_nblk": [_I],
     "b200ad_gn_stats": [_P, _I, _P, _I, _I, _I, _I, _P, _P],
     "b200ad_gn_apply": [_I, _P, _I, _P, _I, _I, _I, _I, _P, _I, _F, _P, _P, _I, _P, _P, _P],
+    "b200ad_group_norm": [_I, _P, _I, _P, _I, _I, _I, _I, _P, _I, _F, _P, _P, _I, _P, _P, _P],
     "b200ad_layernorm": [_I, _P, _I, _I, _P, _P, _F, _P, _I, _I, _P, _P],
     "b200ad_cast": [_I, _P, _I, _I, _I, _I, _I, _P, _P],
     "b200ad_attention": [_I, _P, _L, _P, _L, _P, _L, _I, _I, _I, _I, _I, _I, _I, _P, _L, _P],

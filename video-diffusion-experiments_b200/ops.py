@@ -166,17 +166,14 @@ class Ops:
             assert x1.dtype == torch.float32 and x1.is_contiguous()
         nblk = self.L.b200ad_gn_nblk(hw)
         partial = torch.empty((nimg * nblk * groups + nimg * groups, 2), device=x0.device, dtype=torch.float32)
-        with self._rec("gn_stats", 0.0, _nb(x0, x1)):
-            rc = self.L.b200ad_gn_stats(x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups, partial.data_ptr(),
-                                        _stream())
-        _lib.check(rc, "b200ad_gn_stats")
         out = torch.empty((nimg * hw, c0 + c1), device=x0.device, dtype=self.op_dtype)
         raw = torch.empty_like(out) if want_raw else None
-        with self._rec("gn_apply", 0.0, _nb(x0, x1, out, raw)):
-            rc = self.L.b200ad_gn_apply(self.op, x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups,
-                                        partial.data_ptr(), frames_per_stat, float(eps), gamma.data_ptr(),
-                                        beta.data_ptr(), 1 if silu else 0, out.data_ptr(), _ptr(raw), _stream())
-        _lib.check(rc, "b200ad_gn_apply")
+        # algorithmic bytes: the input twice (statistics, apply) + the operand-typed output(s)
+        with self._rec("group_norm", 0.0, 2 * _nb(x0, x1) + _nb(out, raw)):
+            rc = self.L.b200ad_group_norm(self.op, x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups,
+                                          partial.data_ptr(), frames_per_stat, float(eps), gamma.data_ptr(),
+                                          beta.data_ptr(), 1 if silu else 0, out.data_ptr(), _ptr(raw), _stream())
+        _lib.check(rc, "b200ad_group_norm")
         return (out, raw) if want_raw else out
 
     def layer_norm(self, x, gamma, beta, eps=1e-5, pe=None, hw=1, frames=1):
