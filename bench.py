@@ -340,8 +340,18 @@ def run_b200_arm(args):
                 "roofline": roof, "families": fam, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
+        # Tear-down: the captured CUDA graphs hold the pair communicator (the per-step all-gather is inside the graph);
+        # destroying the process group with them alive hung at exit (first 2-GPU run of this bench: JSON line
+        # printed, torchrun never returned).  Drop the graphs, drain the device, meet once more, then leave without
+        # NCCL's finalizers.
+        for pl in pipe._plans.values():
+            pl.graph = None
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
     return 0
 
 

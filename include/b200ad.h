@@ -70,8 +70,7 @@ int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const float* x1, int 
                     const float* partial, int frames_per_stat, float eps, const float* gamma, const float* beta,
                     int silu, void* out_op, void* raw_op, void* stream);
 
-/* Statistics + apply in one call (same arguments and workspace as the pair above), walked over sub-batches of
- * images sized to the L2 so that the apply pass re-reads its input from L2 instead of HBM. */
+/* Statistics + apply in one call (same arguments and workspace as the pair above). */
 int b200ad_group_norm(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
                       float* partial, int frames_per_stat, float eps, const float* gamma, const float* beta, int silu,
                       void* out_op, void* raw_op, void* stream);
@@ -94,6 +93,15 @@ int b200ad_cast(int op_dtype, const float* x, int nimg, int h, int w, int C, int
 int b200ad_attention(int op_dtype, const void* q, long long ldq, const void* k, long long ldk, const void* v,
                      long long ldv, int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div,
                      void* out_op, long long ldo, void* stream);
+
+/* Same with `flags`.  B200AD_ATTN_V_ONES (1): the caller guarantees V[:, hd*dpad + d] == 1 for every key row and head
+ * (dpad > d), e.g. written by the bias of the GEMM that produced V; the long self-attention kernel then takes the
+ * softmax denominator from the PV product instead of summing the probabilities.  Other kernels ignore the flag (the
+ * ones column only feeds an output pad column that is never stored). */
+#define B200AD_ATTN_V_ONES 1
+int b200ad_attention2(int op_dtype, const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                      long long ldv, int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, int flags,
+                      void* out_op, long long ldo, void* stream);
 
 /* ---- K5: motion-module temporal self-attention over the frame axis, read in place from the (b,f,hw)-ordered
  * rows (no permute copy).  qkv: operand-typed [B*F*hw, 3C] = (q|k|v); out_op [B*F*hw, C]. */

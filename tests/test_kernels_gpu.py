@@ -197,6 +197,30 @@ def test_attention(mode, tol, nb, heads, Lq, Lk, d, dpad, kv_div):
     assert rel(out.cpu(), ref) < tol
 
 
+@pytest.mark.parametrize("nb,heads,L,d,dpad,grow", [(2, 3, 1024, 40, 64, False), (1, 2, 2304, 80, 128, False),
+                                                    (1, 2, 1024, 40, 64, True), (2, 8, 256, 40, 64, False)])
+def test_attention_denominator_from_ones_column(nb, heads, L, d, dpad, grow):
+    """B200AD_ATTN_V_ONES: V's pad column d holds 1.0, the long self-attention kernel takes the softmax denominator
+    from the PV product (incl. across lazy rescales); the short-sequence kernel (L = 256) must simply ignore it."""
+    o = ops("bf16")
+    q = bf(rnd(nb, heads, L, d, seed=21) * (3.0 if grow else 1.0))
+    k = bf(rnd(nb, heads, L, d, seed=22))
+    if grow:
+        k = bf(k * (1.0 + 3.0 * torch.arange(L)[None, None, :, None] / L))
+    v = bf(rnd(nb, heads, L, d, seed=23))
+    ref = _attn_ref(q, k, v).permute(0, 2, 1, 3).reshape(nb * L, heads * d)
+
+    def pack(t, ones=False):
+        p = torch.zeros(nb, L, heads, dpad)
+        p[..., :d] = t.permute(0, 2, 1, 3)
+        if ones:
+            p[..., d] = 1.0
+        return p.reshape(nb * L, heads * dpad).to(DEV, torch.bfloat16)
+
+    out = o.attention(pack(q), pack(k), pack(v, ones=True), nb, heads, L, L, d, dpad, 1, v_ones=True)
+    assert rel(out.cpu(), ref) < (1e-2 if grow else 8e-3)
+
+
 @pytest.mark.parametrize("d,dpad", [(40, 64), (80, 128)])
 def test_attention_lazy_rescale_with_growing_maxima(d, dpad):
     """Ping-pong kernel (attn_fa.cu): scores with a wide range and maxima that keep growing along the key axis, so

@@ -57,6 +57,12 @@ def attention():
         hd = 8 * dp
         us = timeit(lambda: o.attention(qkv[:, :hd], qkv[:, hd:2 * hd], qkv[:, 2 * hd:], 32, 8, L, L, d, dp, 1), 5)
         report(f"self-attention n=32 heads=8 L={L} d={d} (dpad {dp})", us, 4.0 * 32 * 8 * L * L * d, 32 * L * C * 2 * 4)
+        if dp > d and L >= 512:
+            qkv.view(32 * L, 3, 8, dp)[:, 2, :, d] = 1.0            # V pad column d = 1 (B200AD_ATTN_V_ONES)
+            us = timeit(lambda: o.attention(qkv[:, :hd], qkv[:, hd:2 * hd], qkv[:, 2 * hd:], 32, 8, L, L, d, dp, 1,
+                                            v_ones=True), 5)
+            report(f"   same, denominator from the PV product (V ones column)", us, 4.0 * 32 * 8 * L * L * d,
+                   32 * L * C * 2 * 4)
         kv = bf(2 * 77, 2 * hd)
         q = bf(32 * L, hd)
         us = timeit(lambda: o.attention(q, kv[:, :hd], kv[:, hd:], 32, 8, L, 77, d, dp, 16), 5)

@@ -52,7 +52,11 @@ __device__ __forceinline__ float poly_exp2(float x) {
 #endif
 
 // DP: padded head width (64 or 128).  BN: keys per tile (128 for DP=64, 64 for DP=128).
-template <int DP, int BN>
+// VS: the caller guarantees that pad column d of every V row is 1.0 (the QKV GEMM writes it through its bias), so the
+// softmax denominator comes out of the PV MMA as O[:, d] -- the sum of the bf16-ROUNDED probabilities, i.e. exactly
+// the weights the numerator used -- and the 128 FADDs per row and key tile of the explicit row sum disappear
+// (17 % of the softmax loop's instructions, which is issue-bound at d = 40); the lazy rescale covers it for free.
+template <int DP, int BN, bool VS>
 __global__ void __launch_bounds__(FA_THREADS, 1)
 attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ FaParams p) {
@@ -248,7 +252,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         const float x = fmaf(s[i], sc, neg_m);
         s[i] = (B200AD_FA_EMU_EVERY > 0 && (i % B200AD_FA_EMU_EVERY) == B200AD_FA_EMU_EVERY - 1) ? poly_exp2(x)
                                                                                              : fast_exp2(x);
-        sum8[i & 7] += s[i];
+        if (!VS) sum8[i & 7] += s[i];
       }
       const float sum = ((sum8[0] + sum8[1]) + (sum8[2] + sum8[3])) + ((sum8[4] + sum8[5]) + (sum8[6] + sum8[7]));
       // PV(j-1) must be complete before P is overwritten or O rescaled
@@ -289,7 +293,17 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     // ---- epilogue: O / l -> bf16 ----
     mbar_wait(&o_full[t], (p.nkv - 1) & 1);
     tc_fence_after();
-    const float inv = 1.f / l;
+    float inv = 1.f / l;
+    if (VS) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(o_tmem + (uint32_t)(p.d & ~31), r);
+      tmem_wait_ld();
+      float lv = 1.f;
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        if (i == (p.d & 31)) lv = __uint_as_float(r[i]);
+      inv = 1.f / lv;
+    }
     const int qrow = (2 * qt + t) * 128 + row;
     bf16* orow = p.out + ((long long)n * p.Lq + qrow) * p.ldo + hd * p.d;
 #pragma unroll 1
@@ -316,7 +330,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   }
 }
 
-template <int DP, int BN>
+template <int DP, int BN, bool VS>
 static int launch_attn_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                           int nbatch, int heads, int L, int d, void* out, long long ldo, cudaStream_t stream) {
   constexpr int NS = DP / 64;
@@ -344,11 +358,11 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   const size_t smem = (size_t)(2 * NS * 128 * 128 + 2 * 3 * NS * BN * 128 + 2 * (BN / 64) * 128 * 128) + 1024 + 256;  // slabs + alignment + barriers
   static bool attr = false;
   if (!attr) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN, VS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr = true;
   }
   dim3 grid(L / 256, heads, nbatch);
-  attn_fa_kernel<DP, BN><<<grid, FA_THREADS, smem, stream>>>(tmQ, tmK, tmV, p);
+  attn_fa_kernel<DP, BN, VS><<<grid, FA_THREADS, smem, stream>>>(tmQ, tmK, tmV, p);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -356,11 +370,16 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
 
 // Self-attention fast path; returns 1 when the shape is not served here (the caller falls back to attn_tc.cu).
 int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
-                      int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, void* out, long long ldo,
-                      cudaStream_t stream) {
+                      int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, int v_ones, void* out,
+                      long long ldo, cudaStream_t stream) {
   if (Lq != Lk || kv_div != 1 || Lq % 256 != 0 || Lq < 512) return 1;
-  if (dpad == 64) return launch_attn_fa<64, 128>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
-  if (dpad == 128) return launch_attn_fa<128, 64>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
+  const bool vs = v_ones && d < dpad;
+  if (dpad == 64)
+    return vs ? launch_attn_fa<64, 128, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
+              : launch_attn_fa<64, 128, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
+  if (dpad == 128)
+    return vs ? launch_attn_fa<128, 64, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
+              : launch_attn_fa<128, 64, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
   return 1;
 }
 

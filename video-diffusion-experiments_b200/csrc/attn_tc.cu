@@ -15,8 +15,8 @@ int attention_f32_simt(const float* q, long long ldq, const float* k, long long 
                        cudaStream_t stream);   // simt.cu
 
 int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
-                      int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, void* out, long long ldo,
-                      cudaStream_t stream);   // attn_fa.cu: ping-pong kernel for the long self-attention layers
+                      int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, int v_ones, void* out,
+                      long long ldo, cudaStream_t stream);   // attn_fa.cu: ping-pong kernel for the long self-attention layers
 
 static constexpr int ATT_THREADS = 192;
 static constexpr int SLAB = 128 * 128;   // bytes of one [128 rows x 64 bf16] swizzled slab
@@ -284,9 +284,19 @@ static int launch_attn_tc(const void* q, long long ldq, const void* k, long long
 
 using namespace b200ad;
 
+extern "C" int b200ad_attention2(int op_dtype, const void* q, long long ldq, const void* k, long long ldk,
+                                 const void* v, long long ldv, int nbatch, int heads, int Lq, int Lk, int d, int dpad,
+                                 int kv_div, int flags, void* out_op, long long ldo, void* stream);
 extern "C" int b200ad_attention(int op_dtype, const void* q, long long ldq, const void* k, long long ldk,
                                 const void* v, long long ldv, int nbatch, int heads, int Lq, int Lk, int d, int dpad,
                                 int kv_div, void* out_op, long long ldo, void* stream) {
+  return b200ad_attention2(op_dtype, q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, 0, out_op, ldo,
+                           stream);
+}
+
+extern "C" int b200ad_attention2(int op_dtype, const void* q, long long ldq, const void* k, long long ldk,
+                                 const void* v, long long ldv, int nbatch, int heads, int Lq, int Lk, int d, int dpad,
+                                 int kv_div, int flags, void* out_op, long long ldo, void* stream) {
   B200AD_REQUIRE(q && k && v && out_op, "attention: null pointer");
   B200AD_REQUIRE(Lq > 0 && Lk > 0 && d > 0 && d % 2 == 0 && dpad >= d && kv_div >= 1, "attention: bad shape");
   cudaStream_t st = (cudaStream_t)stream;
@@ -297,7 +307,7 @@ extern "C" int b200ad_attention(int op_dtype, const void* q, long long ldq, cons
   B200AD_REQUIRE(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0, "attention: leading dims must be multiples of 8");
   B200AD_REQUIRE((d * 2) % 4 == 0 && (ldo % 2) == 0, "attention: output alignment");
   {
-    const int rc = attention_bf16_fa(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out_op, ldo, st);
+    const int rc = attention_bf16_fa(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, flags & 1, out_op, ldo, st);
     if (rc <= 0) return rc;          // served (0) or failed (<0); 1 = not a shape of the ping-pong kernel
   }
   const bool one_tile = Lk <= 128;

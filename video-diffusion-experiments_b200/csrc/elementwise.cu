@@ -136,6 +136,9 @@ __device__ __forceinline__ float4 gn_load_vec(const float* x0, int c0, const flo
                   : __ldg(reinterpret_cast<const float4*>(x1 + row * c1 + (c - c0)));
 }
 static constexpr int GN_UNROLL = 8;
+static constexpr int GN_SB = 1;            // 32-row sub-blocks per thread block of the vectorised kernels.  4 (128 rows,
+                                           // several load batches per thread) did not help at 64^2 (106.9 vs 106.1 us)
+                                           // and starved the low-resolution levels of blocks (hw = 256: 44 -> 105 us)
 
 __global__ void gn_stats_vec_kernel(const float* __restrict__ x0, int c0, const float* __restrict__ x1, int c1, int hw,
                                     int groups, int R, float2* __restrict__ partial) {
@@ -143,9 +146,9 @@ __global__ void gn_stats_vec_kernel(const float* __restrict__ x0, int c0, const 
   const int C = c0 + c1;
   const int nvec = C >> 2;
   const int cpg = C / groups;
-  const int n = blockIdx.y, blk = blockIdx.x;
+  const int n = blockIdx.y, blk = blockIdx.x * GN_SB;          // first 32-row sub-block of this block
   const int r0 = blk * GN_ROWS_PER_BLOCK;
-  const int r1 = min(hw, r0 + GN_ROWS_PER_BLOCK);
+  const int r1 = min(hw, r0 + GN_SB * GN_ROWS_PER_BLOCK);
   const int v = threadIdx.x % nvec, rl = threadIdx.x / nvec;
   const int c = v * 4;
   const float* base = (c < c0) ? x0 + c : x1 + (c - c0);
@@ -174,7 +177,12 @@ __global__ void gn_stats_vec_kernel(const float* __restrict__ x0, int c0, const 
     float ss = 0.f, qq = 0.f;
     for (int rr = 0; rr < R; ++rr)
       for (int cc = g * cpg; cc < (g + 1) * cpg; ++cc) { const float2 e = sh[(size_t)rr * C + cc]; ss += e.x; qq += e.y; }
-    partial[((long long)n * gridDim.x + blk) * groups + g] = make_float2(ss, qq);
+    // the block's sums go to the slot of its first sub-block, the other slots it covers are zero (the finalize
+    // kernel adds all nblk slots of an image)
+    const int nblk = gn_nblk(hw);
+    partial[((long long)n * nblk + blk) * groups + g] = make_float2(ss, qq);
+    for (int sb = 1; sb < GN_SB && blk + sb < nblk; ++sb)
+      partial[((long long)n * nblk + blk + sb) * groups + g] = make_float2(0.f, 0.f);
   }
 }
 
@@ -187,8 +195,8 @@ __global__ void gn_apply_vec_kernel(const float* __restrict__ x0, int c0, const 
   const int nvec = C >> 2;
   const int cpg = C / groups;
   const int n = blockIdx.y, blk = blockIdx.x;
-  const int r0 = blk * GN_ROWS_PER_BLOCK;
-  const int r1 = min(hw, r0 + GN_ROWS_PER_BLOCK);
+  const int r0 = blk * GN_SB * GN_ROWS_PER_BLOCK;
+  const int r1 = min(hw, r0 + GN_SB * GN_ROWS_PER_BLOCK);
   const int v = threadIdx.x % nvec, rl = threadIdx.x / nvec;
   const int c = v * 4;
   const float2* mr = meanrstd + (n / frames_per_stat) * groups;
@@ -259,7 +267,8 @@ extern "C" int b200ad_gn_stats(const float* x0, int c0, const float* x1, int c1,
   dim3 grid(gn_nblk(hw), nimg);
   if (gn_vec_ok(C, c0, groups)) {
     const int R = gn_vec_R(C);
-    gn_stats_vec_kernel<<<grid, R * (C / 4), (size_t)R * C * sizeof(float2), (cudaStream_t)stream>>>(
+    const dim3 vgrid((gn_nblk(hw) + GN_SB - 1) / GN_SB, nimg);
+    gn_stats_vec_kernel<<<vgrid, R * (C / 4), (size_t)R * C * sizeof(float2), (cudaStream_t)stream>>>(
         x0, c0, x1, c1, hw, groups, R, reinterpret_cast<float2*>(partial));
   } else
     gn_stats_kernel<<<grid, gn_threads(C), (C / 2) * sizeof(float2), (cudaStream_t)stream>>>(
@@ -293,11 +302,12 @@ extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const floa
   }
   if (gn_vec_ok(C, c0, groups)) {
     const int R = gn_vec_R(C);
+    const dim3 vgrid((gn_nblk(hw) + GN_SB - 1) / GN_SB, nimg);
     if (op_dtype == 0)
-      gn_apply_vec_kernel<bf16><<<grid, R * (C / 4), 0, (cudaStream_t)stream>>>(
+      gn_apply_vec_kernel<bf16><<<vgrid, R * (C / 4), 0, (cudaStream_t)stream>>>(
           x0, c0, x1, c1, hw, groups, R, meanrstd, frames_per_stat, gamma, beta, silu, (bf16*)out_op, (bf16*)raw_op);
     else
-      gn_apply_vec_kernel<float><<<grid, R * (C / 4), 0, (cudaStream_t)stream>>>(
+      gn_apply_vec_kernel<float><<<vgrid, R * (C / 4), 0, (cudaStream_t)stream>>>(
           x0, c0, x1, c1, hw, groups, R, meanrstd, frames_per_stat, gamma, beta, silu, (float*)out_op, (float*)raw_op);
   } else if (op_dtype == 0)
     gn_apply_kernel<bf16><<<grid, gn_threads(C), 0, (cudaStream_t)stream>>>(
@@ -310,9 +320,9 @@ extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const floa
   return 0;
 }
 
-// Fused GroupNorm: statistics + finalize + apply in one call, walked over sub-batches of images that fit the L2
-// (the apply pass of a sub-batch re-reads what its statistics pass just pulled into the 126 MB L2; with two whole-
-// tensor passes the 168-503 MB level-0 tensors were read from HBM twice).  Same workspace layout as gn_stats/gn_apply.
+// Fused GroupNorm: statistics + finalize + apply in one call (same workspace layout as gn_stats/gn_apply).  Optionally
+// (B200AD_GN_L2_WALK) walked over sub-batches of images that fit the L2, so that the apply pass re-reads its input
+// from L2 instead of HBM.
 extern "C" int b200ad_group_norm(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
                                  int groups, float* partial, int frames_per_stat, float eps, const float* gamma,
                                  const float* beta, int silu, void* out_op, void* raw_op, void* stream) {
@@ -323,7 +333,11 @@ extern "C" int b200ad_group_norm(int op_dtype, const float* x0, int c0, const fl
   const double img_bytes = (double)hw * C * 4.0;
   const double budget = 56e6;                       // fp32 input bytes per sub-batch (its bf16 output shares the L2)
   int chunk = nimg;
-  if (img_bytes * nimg > 72e6) {
+  // Measured on B200 (profiles/kbench_r01j.txt): the sub-batched walk is SLOWER than two whole-tensor passes
+  // (145 vs 106 us at 32 x 64^2 x 320: eight small launch triples do not fill the machine and pay launch gaps), so
+  // it stays opt-in for experiments.
+  static const bool l2_walk = getenv("B200AD_GN_L2_WALK") != nullptr;
+  if (l2_walk && img_bytes * nimg > 72e6) {
     chunk = (int)(budget / img_bytes);
     if (chunk < frames_per_stat) chunk = frames_per_stat;
     chunk -= chunk % frames_per_stat;

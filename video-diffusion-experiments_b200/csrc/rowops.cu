@@ -6,16 +6,14 @@ namespace b200ad {
 
 // ----------------------------------------------------------------------------- LayerNorm (+PE)
 // One warp per LN_ROWS rows, the rows live in registers (float2 per lane, lane-strided => coalesced 256 B requests).
-// Two rows per warp: both rows' loads are issued before the first reduction and the two shuffle chains interleave
-// (one row per warp left ~1.3 KB in flight per warp and two serial 5-step shuffle reductions: 4.0-4.5 TB/s).
-static constexpr int LN_ROWS = 2;
+static constexpr int LN_ROWS = 1;   // 2 measured slower in the step (4.8 vs 3.4 ms over 111 launches): fewer warps in flight
 template <typename T, int MAXP>   // MAXP = max float2 per lane  (C <= 64*MAXP)
 __global__ void layernorm_kernel(const float* __restrict__ x, int rows, int C, const float* __restrict__ gamma,
                                  const float* __restrict__ beta, float eps, const float* __restrict__ pe, int hw,
                                  int frames, T* __restrict__ out) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  const long long row0 = (long long)warp * LN_ROWS;
+  const int row0 = warp * LN_ROWS;
   if (row0 >= rows) return;
   const int npairs = C >> 1;
   float2 v[LN_ROWS][MAXP];
@@ -24,7 +22,7 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows, int C, c
   for (int r = 0; r < LN_ROWS; ++r) {
     s[r] = 0.f;
     const bool live = row0 + r < rows;
-    const float* xr = x + (row0 + (live ? r : 0)) * C;
+    const float* xr = x + (long long)(row0 + (live ? r : 0)) * C;
 #pragma unroll
     for (int j = 0; j < MAXP; ++j) {
       const int pr = lane + 32 * j;
@@ -58,22 +56,26 @@ __global__ void layernorm_kernel(const float* __restrict__ x, int rows, int C, c
     for (int r = 0; r < LN_ROWS; ++r) q[r] += __shfl_xor_sync(0xffffffffu, q[r], o);
 #pragma unroll
   for (int r = 0; r < LN_ROWS; ++r) rstd[r] = rsqrtf(q[r] / (float)C + eps);
+  const float* per[LN_ROWS];
+#pragma unroll
+  for (int r = 0; r < LN_ROWS; ++r)
+    per[r] = pe ? pe + (long long)((int)((row0 + r) / hw) % frames) * C : nullptr;
 #pragma unroll
   for (int j = 0; j < MAXP; ++j) {
     const int pr = lane + 32 * j;
     if (pr < npairs) {
-      const float2 g = __ldg(reinterpret_cast<const float2*>(gamma + 2 * pr));
-      const float2 b = __ldg(reinterpret_cast<const float2*>(beta + 2 * pr));
+      const float2 g = *reinterpret_cast<const float2*>(gamma + 2 * pr);
+      const float2 b = *reinterpret_cast<const float2*>(beta + 2 * pr);
 #pragma unroll
       for (int r = 0; r < LN_ROWS; ++r) {
         if (row0 + r >= rows) break;
         float a0 = (v[r][j].x - mean[r]) * rstd[r] * g.x + b.x;
         float a1 = (v[r][j].y - mean[r]) * rstd[r] * g.y + b.y;
-        if (pe) {
-          const float2 p2 = __ldg(reinterpret_cast<const float2*>(pe + (long long)(((row0 + r) / hw) % frames) * C + 2 * pr));
+        if (per[r]) {
+          const float2 p2 = *reinterpret_cast<const float2*>(per[r] + 2 * pr);
           a0 += p2.x; a1 += p2.y;
         }
-        store2<T>(out + (row0 + r) * C + 2 * pr, a0, a1);
+        store2<T>(out + (long long)(row0 + r) * C + 2 * pr, a0, a1);
       }
     }
   }

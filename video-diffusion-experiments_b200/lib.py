@@ -32,6 +32,7 @@ SIGNATURES = {
     "b200ad_layernorm": [_I, _P, _I, _I, _P, _P, _F, _P, _I, _I, _P, _P],
     "b200ad_cast": [_I, _P, _I, _I, _I, _I, _I, _P, _P],
     "b200ad_attention": [_I, _P, _L, _P, _L, _P, _L, _I, _I, _I, _I, _I, _I, _I, _P, _L, _P],
+    "b200ad_attention2": [_I, _P, _L, _P, _L, _P, _L, _I, _I, _I, _I, _I, _I, _I, _I, _P, _L, _P],
     "b200ad_temporal_attention": [_I, _P, _I, _I, _I, _I, _I, _P, _P],
     "b200ad_timestep_sinusoid": [_P, _I, _I, _P, _P],
     "b200ad_small_linear": [_P, _I, _I, _P, _P, _I, _I, _I, _P, _P],

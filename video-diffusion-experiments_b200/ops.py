@@ -132,17 +132,18 @@ class Ops:
         _lib.check(rc, "b200ad_conv3x3")
         return out_f32, out_op
 
-    def attention(self, q, k, v, nbatch, heads, Lq, Lk, d, dpad, kv_div=1):
-        """q/k/v: 2-D operand-typed views (row stride = leading dim).  Returns [nbatch*Lq, heads*d]."""
+    def attention(self, q, k, v, nbatch, heads, Lq, Lk, d, dpad, kv_div=1, v_ones=False):
+        """q/k/v: 2-D operand-typed views (row stride = leading dim).  Returns [nbatch*Lq, heads*d].
+        v_ones: pad column d of every head of v holds 1.0 (B200AD_ATTN_V_ONES)."""
         _need_cuda(q, k, v)
         out = torch.empty((nbatch * Lq, heads * d), device=q.device, dtype=self.op_dtype)
         es = out.element_size()
         nbytes = es * heads * d * (2.0 * nbatch * Lq + 2.0 * (nbatch // kv_div) * Lk)
         with self._rec("attention_L%d_d%d" % (Lk, d), 4.0 * nbatch * heads * Lq * Lk * d, nbytes):
-            rc = self.L.b200ad_attention(self.op, q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(),
-                                         v.stride(0), nbatch, heads, Lq, Lk, d, dpad, kv_div, out.data_ptr(),
-                                         out.stride(0), _stream())
-        _lib.check(rc, "b200ad_attention")
+            rc = self.L.b200ad_attention2(self.op, q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(),
+                                          v.stride(0), nbatch, heads, Lq, Lk, d, dpad, kv_div, 1 if v_ones else 0,
+                                          out.data_ptr(), out.stride(0), _stream())
+        _lib.check(rc, "b200ad_attention2")
         return out
 
     def temporal_attention(self, qkv, B, F, hw, C, heads):

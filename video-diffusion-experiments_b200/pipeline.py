@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import hashlib
 import os
+import sys
 from dataclasses import dataclass
 from typing import List, Optional, Union
 
@@ -27,7 +28,7 @@ from .vae import AutoencoderKLDecoder
 
 
 def _log(msg: str):
-    print(f"[b200ad] {msg}", flush=True)
+    print(f"[b200ad] {msg}", file=sys.stderr, flush=True)      # stdout stays clean (bench.py prints one JSON line)
 
 
 @dataclass

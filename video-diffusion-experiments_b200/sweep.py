@@ -239,8 +239,15 @@ def main(argv=None) -> int:
                           "videos_per_hour": nruns * 3600 / secs if secs else None, "n_gpus": world,
                           "workers": n_workers, "gpus_per_worker": per}), flush=True)
     if world > 1:
+        # captured graphs hold the pair communicator: drop them and leave without NCCL's finalizers (see bench.py)
+        for pl in pipe._plans.values():
+            pl.graph = None
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        import sys
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
     return 0
 
 

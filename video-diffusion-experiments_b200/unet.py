@@ -139,6 +139,14 @@ class Attention(_Packable):
                            _pad_heads(self.to_k.weight.detach(), self.heads, dp),
                            _pad_heads(self.to_v.weight.detach(), self.heads, dp)], 0)
             p["wqkv"], p["dp"] = _dev_w(o, w), dp
+            # V pad column d of every head = 1.0 (zero weight row + bias 1): the long self-attention kernel reads
+            # its softmax denominator out of the PV product (B200AD_ATTN_V_ONES)
+            d = self.query_dim // self.heads
+            p["bqkv"] = None
+            if dp > d:
+                b = torch.zeros(3, self.heads, dp)
+                b[2, :, d] = 1.0
+                p["bqkv"] = _dev_f(b.reshape(-1))
         return p
 
     def packed_cross(self, o: Ops):
@@ -163,9 +171,10 @@ class Attention(_Packable):
         o = st.o
         p = self.packed_spatial_self(o)
         H, C, dp = self.heads, self.query_dim, p["dp"]
-        _, qkv = o.gemm(n_op, p["wqkv"], want_op=True)
+        _, qkv = o.gemm(n_op, p["wqkv"], bias=p["bqkv"], want_op=True)
         hd = H * dp
-        att = o.attention(qkv[:, :hd], qkv[:, hd:2 * hd], qkv[:, 2 * hd:], nimg, H, L, L, C // H, dp, 1)
+        att = o.attention(qkv[:, :hd], qkv[:, hd:2 * hd], qkv[:, 2 * hd:], nimg, H, L, L, C // H, dp, 1,
+                          v_ones=p["bqkv"] is not None)
         o.gemm(att, p["wo"], bias=p["bo"], residual=h, out_f32=h)
         return h
 
