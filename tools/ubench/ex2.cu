@@ -21,7 +21,18 @@ __global__ void k(uint32_t* out, float seed) {
       if (MODE == 0) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(x[i]));
       if (MODE == 1) asm volatile("ex2.approx.ftz.bf16x2 %0, %0;" : "+r"(h[i]));
       if (MODE == 2) asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(h[i]));
-      if (MODE == 3) asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h[i]) : "f"(x[i]), "f"(x[(i + 1) % ILP]));
+      if (MODE == 3) {   // F2FP pack with a data dependence (h feeds back into x) so it cannot be hoisted
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h[i]) : "f"(x[i]), "f"(x[(i + 1) % ILP]));
+        x[i] = __uint_as_float(h[i]);
+      }
+      if (MODE == 6) {   // pack by truncation: PRMT of the two high halves
+        asm volatile("prmt.b32 %0, %1, %2, 0x7632;" : "=r"(h[i]) : "r"(__float_as_uint(x[i])), "r"(__float_as_uint(x[(i + 1) % ILP])));
+        x[i] = __uint_as_float(h[i]);
+      }
+      if (MODE == 7) {   // 3-input max
+        x[i] = fmaxf(fmaxf(x[i], x[(i + 1) % ILP]), x[(i + 2) % ILP]);
+      }
+      if (MODE == 8) asm volatile("tanh.approx.f32 %0, %0;" : "+f"(x[i]));
       if (MODE == 4) {  // Cody-Waite + cubic on the FMA/ALU pipes (one element)
         float t = x[i];
         float fl = floorf(t);
@@ -72,6 +83,9 @@ int main() {
   run<3>("cvt.rn.bf16x2.f32 (pack 2)", 2, out, p.multiProcessorCount, khz);
   run<4>("poly3 exp2 (FMA pipe)", 1, out, p.multiProcessorCount, khz);
   run<5>("2x fma + pack + ex2.bf16x2", 2, out, p.multiProcessorCount, khz);
+  run<6>("prmt pack by truncation (pack 2)", 2, out, p.multiProcessorCount, khz);
+  run<7>("fmax3", 2, out, p.multiProcessorCount, khz);
+  run<8>("tanh.approx.f32", 1, out, p.multiProcessorCount, khz);
   cudaError_t e = cudaDeviceSynchronize();
   printf("status: %s\n", cudaGetErrorString(e));
   return e != cudaSuccess;

@@ -19,10 +19,12 @@
 
 namespace b200ad {
 
-static constexpr int FA_THREADS = 384;
+// threads per CTA: 8*TPR softmax warps + one warpgroup holding the TMA producer, the UMMA issuer and two idle warps
+__host__ __device__ constexpr int fa_threads(int tpr) { return (8 * tpr + 4) * 32; }
 
 struct FaParams {
   int Lq, Lk, d, nkv;
+  int stagger;             // anti-phase schedule of the two query tiles (see the UMMA issuer)
   int dk16;                // k-steps of 16 for Q K^T
   float scale_log2;        // d^-1/2 * log2(e)
   bf16* out;
@@ -47,6 +49,22 @@ __device__ __forceinline__ float poly_exp2(float x) {
   r = fmaf(r, f, 1.0f);
   return __int_as_float(__float_as_int(r) + (__float_as_int(j) << 23));
 }
+// Probabilities -> bf16 pair.  With the V-ones-column denominator (VS) numerator and denominator are sums of the SAME
+// bf16 values, so a truncating pack (one PRMT on the ALU pipe instead of F2FP) only shifts every P by the same
+// relative bias, which the normalisation cancels; the remaining rounding noise has the variance of round-to-nearest.
+// Opt-in (-DB200AD_FA_TRUNC_P=1) until measured.
+#ifndef B200AD_FA_TRUNC_P
+#define B200AD_FA_TRUNC_P 0
+#endif
+template <bool VS>
+__device__ __forceinline__ uint32_t pack_p(float lo, float hi) {
+  if (VS && B200AD_FA_TRUNC_P) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, 0x7632;" : "=r"(r) : "r"(__float_as_uint(lo)), "r"(__float_as_uint(hi)));
+    return r;
+  }
+  return pack_bf16x2(lo, hi);
+}
 #ifndef B200AD_FA_EMU_EVERY
 #define B200AD_FA_EMU_EVERY 8      // every 8th exponential runs on the FMA pipes instead of the MUFU unit
 #endif
@@ -56,8 +74,13 @@ __device__ __forceinline__ float poly_exp2(float x) {
 // softmax denominator comes out of the PV MMA as O[:, d] -- the sum of the bf16-ROUNDED probabilities, i.e. exactly
 // the weights the numerator used -- and the 128 FADDs per row and key tile of the explicit row sum disappear
 // (17 % of the softmax loop's instructions, which is issue-bound at d = 40); the lazy rescale covers it for free.
-template <int DP, int BN, bool VS>
-__global__ void __launch_bounds__(FA_THREADS, 1)
+// TPR: softmax threads per score row.  1: one thread holds the whole BN-wide score row (8 softmax warps, two per
+// scheduler: the loop is bound by MUFU / dependency latency, profiles/ncu_full_r01f.md).  2: two threads split the
+// row's columns (16 softmax warps, four per scheduler, 104 registers each); they exchange the row maximum through
+// shared memory once per key tile (double-buffered by tile parity, one named barrier per query tile) and split the O
+// columns of the lazy rescale and of the final normalisation.
+template <int DP, int BN, bool VS, int TPR>
+__global__ void __launch_bounds__(fa_threads(TPR), 1)
 attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ FaParams p) {
   constexpr int NS = DP / 64;                    // 64-column slabs per operand row
@@ -83,13 +106,16 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   uint64_t* p_full = s_full + 2;                       // [2]  128 arrivals
   uint64_t* o_full = p_full + 2;                       // [2]
   uint64_t* s_read = o_full + 2;                       // [2]  128 arrivals: the S tile is in registers
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_read + 2);
+  uint64_t* stag = s_read + 2;                         // [1]  tile A's first exponent phase is over (stagger)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stag + 1);
+  float* smx = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2 parities][2 tiles][TPR][128]
+  constexpr int PW = 8 * TPR, MW = 8 * TPR + 1;        // producer / UMMA-issuer warp
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int qt = blockIdx.x, hd = blockIdx.y, n = blockIdx.z;     // qt: pair of 128-row query tiles
 
-  if (warp == 8 && lane == 0) {
+  if (warp == PW && lane == 0) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
@@ -97,13 +123,14 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     for (int s = 0; s < NST; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&s_full[s], 1);
-      mbar_init(&p_full[s], 128);
+      mbar_init(&p_full[s], 128 * TPR);
       mbar_init(&o_full[s], 1);
-      mbar_init(&s_read[s], 128);
+      mbar_init(&s_read[s], 128 * TPR);
     }
+    mbar_init(stag, 128 * TPR);
     fence_barrier_init();
   }
-  if (warp == 9) {
+  if (warp == MW) {
     tmem_alloc(tmem_slot, TMEM_COLS);
     tmem_relinquish();
   }
@@ -112,9 +139,9 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp >= 8) {
+  if (warp >= PW) {
   asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-  if (warp == 8) {
+  if (warp == PW) {
     // ===================== TMA producer (whole warp loops; one elected lane issues) =====================
     if (elect_one()) {
       mbar_arrive_expect_tx(q_full, 2 * NS * QSLAB);
@@ -140,7 +167,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       __syncwarp();
       if (++st == NST) { st = 0; ph ^= 1; }
     }
-  } else if (warp == 9) {
+  } else if (warp == MW) {
     // ===================== UMMA issuer =====================
     const uint32_t idesc_s = umma_idesc((uint32_t)BN, false, 1u);
     const uint32_t idesc_o = umma_idesc((uint32_t)DP, true, 1u);
@@ -176,13 +203,42 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     tc_fence_after();
     issue_s(0, 0);
     issue_s(1, 0);
-    int st = 0;
+    int st = 0, st_prev = 0;
     uint32_t ph = 0;
     for (int j = 0; j < p.nkv; ++j) {
       int st_n = st + 1;
       uint32_t ph_n = ph;
       if (st_n == NST) { st_n = 0; ph_n ^= 1; }
       const bool more = (j + 1 < p.nkv);
+      if (p.stagger) {
+        // Anti-phase schedule: tile B runs half a key tile behind tile A (its first exponent phase waits for A's), so
+        // that one tile's MUFU-bound exponent phase overlaps the other's max / pack / store phases instead of both
+        // contending for the 16 ex2 / clk / SM at the same time.  The issue order follows that timeline:
+        //   S_A(j+1), PV_B(j-1), S_B(j+1), PV_A(j)
+        if (more) {
+          mbar_wait(&kv_full[st_n], ph_n);
+          mbar_wait(&s_read[0], j & 1);
+          tc_fence_after();
+          issue_s(0, st_n);
+        }
+        if (j > 0) {
+          mbar_wait(&p_full[1], (j - 1) & 1);
+          tc_fence_after();
+          issue_pv(1, st_prev, j == 1, true);
+        }
+        if (more) {
+          mbar_wait(&s_read[1], j & 1);
+          tc_fence_after();
+          issue_s(1, st_n);
+        }
+        mbar_wait(&p_full[0], j & 1);
+        tc_fence_after();
+        issue_pv(0, st, j == 0, false);
+        st_prev = st;
+        st = st_n;
+        ph = ph_n;
+        continue;
+      }
       if (more) {
         // S_t(j+1) as soon as the softmax threads of tile t hold S_t(j) in registers: the next score tile is
         // ready before they finish their exponentials
@@ -203,15 +259,24 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       st = st_n;
       ph = ph_n;
     }
+    if (p.stagger) {
+      mbar_wait(&p_full[1], (p.nkv - 1) & 1);
+      tc_fence_after();
+      issue_pv(1, st_prev, p.nkv == 1, true);
+    }
   }
   } else {
-    // ===================== softmax: warps 0..3 -> tile A, warps 4..7 -> tile B; one thread per query row ====
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
-    const int t = warp >> 2;
+    // ===================== softmax: 4*TPR warps per query tile; TPR threads share a query row ====
+    if (TPR == 1) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");   // 512*104 + 128*40 <= 640*96 (the CTA's own allocation)
+    constexpr int HC = BN / TPR;                 // score columns per thread
+    constexpr int OC = DP / TPR;                 // O columns per thread (rescale, normalisation)
+    const int t = warp / (4 * TPR);
+    const int hf = (warp >> 2) % TPR;            // which part of the row's columns
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
-    const uint32_t s_tmem = tmem_base + lane_addr + (t ? S_COL1 : S_COL0);
+    const uint32_t s_tmem = tmem_base + lane_addr + (t ? S_COL1 : S_COL0) + (uint32_t)(hf * HC);
     const uint32_t o_tmem = tmem_base + lane_addr + (t ? O_COL1 : O_COL0);
     const uint32_t p_row = smem_u32(sP + t * PS * QSLAB) + (uint32_t)(row * 128);
     const int sw = row & 7;
@@ -221,39 +286,49 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     for (int j = 0; j < p.nkv; ++j) {
       mbar_wait(&s_full[t], j & 1);
       tc_fence_after();
-      float s[BN];
+      float s[HC];
 #pragma unroll
-      for (int c = 0; c < BN; c += 32) tmem_ld_32x32b_x32(s_tmem + c, reinterpret_cast<uint32_t*>(s + c));
+      for (int c = 0; c < HC; c += 32) tmem_ld_32x32b_x32(s_tmem + c, reinterpret_cast<uint32_t*>(s + c));
       tmem_wait_ld();
       tc_fence_before();
       mbar_arrive(&s_read[t]);
-      const int kbase = j * BN;
-      if (kbase + BN > p.Lk) {
+      const int kbase = j * BN + hf * HC;
+      if (kbase + HC > p.Lk) {
 #pragma unroll
-        for (int i = 0; i < BN; ++i)
+        for (int i = 0; i < HC; ++i)
           if (kbase + i >= p.Lk) s[i] = -INFINITY;
       }
-      // 8 independent chains: a single max / sum chain is 128 dependent 4-cycle ops per row
+      // 8 independent chains: a single max / sum chain is HC dependent 4-cycle ops per row
       float mx8[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) mx8[i] = s[i];
 #pragma unroll
-      for (int i = 8; i < BN; ++i) mx8[i & 7] = fmaxf(mx8[i & 7], s[i]);
+      for (int i = 8; i < HC; ++i) mx8[i & 7] = fmaxf(mx8[i & 7], s[i]);
       float mx = fmaxf(fmaxf(fmaxf(mx8[0], mx8[1]), fmaxf(mx8[2], mx8[3])),
                        fmaxf(fmaxf(mx8[4], mx8[5]), fmaxf(mx8[6], mx8[7])));
+      if (TPR == 2) {
+        // row maximum across the two column halves: both threads of a row end up with the same value, hence the
+        // same rescale decision and the same reference maximum
+        float* slot = smx + (((j & 1) * 2 + t) * 2) * 128;
+        slot[hf * 128 + row] = mx;
+        named_bar_sync(1 + t, 128 * TPR);
+        mx = fmaxf(mx, slot[(hf ^ 1) * 128 + row]);
+      }
       mx *= sc;
+      if (p.stagger && j == 0 && t == 1) mbar_wait(stag, 0);      // tile B starts its exponentials after tile A's
       // lazy rescale: keep the old reference maximum unless this row's maximum grew by more than 2^8
       const bool need = mx > m_used + 8.0f;
       const float m_new = need ? mx : m_used;
       const float neg_m = -m_new;
       float sum8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int i = 0; i < BN; ++i) {
+      for (int i = 0; i < HC; ++i) {
         const float x = fmaf(s[i], sc, neg_m);
         s[i] = (B200AD_FA_EMU_EVERY > 0 && (i % B200AD_FA_EMU_EVERY) == B200AD_FA_EMU_EVERY - 1) ? poly_exp2(x)
                                                                                              : fast_exp2(x);
         if (!VS) sum8[i & 7] += s[i];
       }
+      if (p.stagger && j == 0 && t == 0) mbar_arrive(stag);
       const float sum = ((sum8[0] + sum8[1]) + (sum8[2] + sum8[3])) + ((sum8[4] + sum8[5]) + (sum8[6] + sum8[7]));
       // PV(j-1) must be complete before P is overwritten or O rescaled
       if (j > 0) {
@@ -263,7 +338,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       if (__any_sync(0xffffffffu, need) && j > 0) {
         const float alpha = need ? fast_exp2(m_used - m_new) : 1.0f;
 #pragma unroll 1
-        for (int c = 0; c < DP; c += 32) {
+        for (int c = hf * OC; c < (hf + 1) * OC; c += 32) {
           uint32_t r[32];
           tmem_ld_32x32b_x32(o_tmem + c, r);
           tmem_wait_ld();
@@ -278,12 +353,13 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       l += sum;
       // bf16 P row -> swizzled smem: 8 keys per 16-byte chunk, chunk index XOR (row & 7) inside each 64-key slab
 #pragma unroll
-      for (int c8 = 0; c8 < BN / 8; ++c8) {
-        const int slab = c8 >> 3, chunk = (c8 & 7) ^ sw;
+      for (int c8 = 0; c8 < HC / 8; ++c8) {
+        const int g8 = hf * (HC / 8) + c8;       // 8-key group within the BN-wide tile
+        const int slab = g8 >> 3, chunk = (g8 & 7) ^ sw;
         const uint32_t a = p_row + (uint32_t)(slab * QSLAB + chunk * 16);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_bf16x2(s[8 * c8], s[8 * c8 + 1])),
-                     "r"(pack_bf16x2(s[8 * c8 + 2], s[8 * c8 + 3])), "r"(pack_bf16x2(s[8 * c8 + 4], s[8 * c8 + 5])),
-                     "r"(pack_bf16x2(s[8 * c8 + 6], s[8 * c8 + 7]))
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(pack_p<VS>(s[8 * c8], s[8 * c8 + 1])),
+                     "r"(pack_p<VS>(s[8 * c8 + 2], s[8 * c8 + 3])), "r"(pack_p<VS>(s[8 * c8 + 4], s[8 * c8 + 5])),
+                     "r"(pack_p<VS>(s[8 * c8 + 6], s[8 * c8 + 7]))
                      : "memory");
       }
       fence_proxy_async_smem();
@@ -293,6 +369,13 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     // ---- epilogue: O / l -> bf16 ----
     mbar_wait(&o_full[t], (p.nkv - 1) & 1);
     tc_fence_after();
+    if (TPR == 2 && !VS) {
+      // the two halves of a row each summed their own probabilities
+      float* slot = smx + ((p.nkv & 1) * 2 + t) * 2 * 128;
+      slot[hf * 128 + row] = l;
+      named_bar_sync(1 + t, 128 * TPR);
+      l += slot[(hf ^ 1) * 128 + row];
+    }
     float inv = 1.f / l;
     if (VS) {
       uint32_t r[32];
@@ -307,7 +390,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const int qrow = (2 * qt + t) * 128 + row;
     bf16* orow = p.out + ((long long)n * p.Lq + qrow) * p.ldo + hd * p.d;
 #pragma unroll 1
-    for (int c = 0; c < DP; c += 32) {
+    for (int c = hf * OC; c < (hf + 1) * OC; c += 32) {
       uint32_t r[32];
       tmem_ld_32x32b_x32(o_tmem + c, r);
       tmem_wait_ld();
@@ -324,13 +407,13 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) {
+  if (warp == MW) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
-template <int DP, int BN, bool VS>
+template <int DP, int BN, bool VS, int TPR>
 static int launch_attn_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                           int nbatch, int heads, int L, int d, void* out, long long ldo, cudaStream_t stream) {
   constexpr int NS = DP / 64;
@@ -351,18 +434,23 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   FaParams p;
   p.Lq = L; p.Lk = L; p.d = d;
   p.nkv = (L + BN - 1) / BN;
+  // measured (profiles/kbench_attention_variants_r01.txt): 1.82-2.08 ms with the anti-phase schedule vs 1.99-2.04 ms
+  // without on the same box at L=4096 d=40, and 2.34 ms per layer inside the step -> off by default
+  static const int stagger = getenv("B200AD_FA_STAGGER") ? atoi(getenv("B200AD_FA_STAGGER")) : 0;
+  p.stagger = stagger;
   p.dk16 = (d + 15) / 16;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)d);
   p.out = reinterpret_cast<bf16*>(out);
   p.ldo = ldo;
-  const size_t smem = (size_t)(2 * NS * 128 * 128 + 2 * 3 * NS * BN * 128 + 2 * (BN / 64) * 128 * 128) + 1024 + 256;  // slabs + alignment + barriers
+  // slabs + alignment + barriers + row-maximum exchange of the two-threads-per-row variant
+  const size_t smem = (size_t)(2 * NS * 128 * 128 + 2 * 3 * NS * BN * 128 + 2 * (BN / 64) * 128 * 128) + 1024 + 256 + 4096;
   static bool attr = false;
   if (!attr) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN, VS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN, VS, TPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr = true;
   }
   dim3 grid(L / 256, heads, nbatch);
-  attn_fa_kernel<DP, BN, VS><<<grid, FA_THREADS, smem, stream>>>(tmQ, tmK, tmV, p);
+  attn_fa_kernel<DP, BN, VS, TPR><<<grid, fa_threads(TPR), smem, stream>>>(tmQ, tmK, tmV, p);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -374,12 +462,20 @@ int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk
                       long long ldo, cudaStream_t stream) {
   if (Lq != Lk || kv_div != 1 || Lq % 256 != 0 || Lq < 512) return 1;
   const bool vs = v_ones && d < dpad;
-  if (dpad == 64)
-    return vs ? launch_attn_fa<64, 128, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
-              : launch_attn_fa<64, 128, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
-  if (dpad == 128)
-    return vs ? launch_attn_fa<128, 64, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
-              : launch_attn_fa<128, 64, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
+  // A/B switch for kbench.  Two threads per row measured no faster than one (1.91 vs 1.87 ms at L=4096 d=40): the
+  // loop is not latency-bound, so the simpler variant stays the default.
+  static const int tpr = getenv("B200AD_FA_TPR") ? atoi(getenv("B200AD_FA_TPR")) : 1;
+#define FA_LAUNCH(DPV, BNV)                                                                                         \
+  do {                                                                                                              \
+    if (tpr == 1)                                                                                                   \
+      return vs ? launch_attn_fa<DPV, BNV, true, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)  \
+                : launch_attn_fa<DPV, BNV, false, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream); \
+    return vs ? launch_attn_fa<DPV, BNV, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)    \
+              : launch_attn_fa<DPV, BNV, false, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);  \
+  } while (0)
+  if (dpad == 64) FA_LAUNCH(64, 128);
+  if (dpad == 128) FA_LAUNCH(128, 64);
+#undef FA_LAUNCH
   return 1;
 }
 

@@ -547,11 +547,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               const float4 b0 = bias_t ? __ldg(bp + j) : z4, b1 = bias_t ? __ldg(bp + 8 + j) : z4;
-              v[2 * j] = (__uint_as_float(acc[4 * j]) + b0.x) * gelu_fast_f(__uint_as_float(acc[4 * j + 1]) + b0.y);
-              v[2 * j + 1] = (__uint_as_float(acc[4 * j + 2]) + b0.z) * gelu_fast_f(__uint_as_float(acc[4 * j + 3]) + b0.w);
-              v[16 + 2 * j] = (__uint_as_float(acc2[4 * j]) + b1.x) * gelu_fast_f(__uint_as_float(acc2[4 * j + 1]) + b1.y);
+              v[2 * j] = (__uint_as_float(acc[4 * j]) + b0.x) * gelu_tanhfit_f(__uint_as_float(acc[4 * j + 1]) + b0.y);
+              v[2 * j + 1] = (__uint_as_float(acc[4 * j + 2]) + b0.z) * gelu_tanhfit_f(__uint_as_float(acc[4 * j + 3]) + b0.w);
+              v[16 + 2 * j] = (__uint_as_float(acc2[4 * j]) + b1.x) * gelu_tanhfit_f(__uint_as_float(acc2[4 * j + 1]) + b1.y);
               v[17 + 2 * j] =
-                  (__uint_as_float(acc2[4 * j + 2]) + b1.z) * gelu_fast_f(__uint_as_float(acc2[4 * j + 3]) + b1.w);
+                  (__uint_as_float(acc2[4 * j + 2]) + b1.z) * gelu_tanhfit_f(__uint_as_float(acc2[4 * j + 3]) + b1.w);
             }
           } else {
 #pragma unroll
