@@ -52,12 +52,16 @@ static void fill_epilogue(Epilogue& e, const float* bias, const float* row_bias,
 
 }  // namespace b200ad
 
-namespace b200ad { void set_gemm_debug_buffer(long long* p); }
+namespace b200ad { void set_gemm_debug_buffer(long long* p); void set_fa_debug_buffer(long long* p); }
 using namespace b200ad;
 
 extern "C" {
 
-int b200ad_debug_buffer(void* dev_i64) { set_gemm_debug_buffer((long long*)dev_i64); return 0; }
+int b200ad_debug_buffer(void* dev_i64) {
+  set_gemm_debug_buffer((long long*)dev_i64);
+  set_fa_debug_buffer((long long*)dev_i64);
+  return 0;
+}
 
 const char* b200ad_last_error(void) { return g_err; }
 int b200ad_version(void) { return 100; }

@@ -22,9 +22,19 @@ namespace b200ad {
 // threads per CTA: 8*TPR softmax warps + one warpgroup holding the TMA producer, the UMMA issuer and two idle warps
 __host__ __device__ constexpr int fa_threads(int tpr) { return (8 * tpr + 4) * 32; }
 
+// Cycle counters of the softmax loop for tools/fa_waits.py (compiled in with -DB200AD_GEMM_PROFILE only).
+#ifdef B200AD_GEMM_PROFILE
+__device__ __forceinline__ long long fa_clock() { return clock64(); }
+#else
+__device__ __forceinline__ long long fa_clock() { return 0; }
+#endif
+static long long* g_fa_dbg = nullptr;
+void set_fa_debug_buffer(long long* p) { g_fa_dbg = p; }
+
 struct FaParams {
+  long long* dbg;          // optional [8] counters of CTA (0,0,0), tile A, warp 0 (null in production)
   int Lq, Lk, d, nkv;
-  int stagger;             // anti-phase schedule of the two query tiles (see the UMMA issuer)
+  int stagger;             // tile B starts its first exponent phase after tile A's (initial anti-phase offset)
   int dk16;                // k-steps of 16 for Q K^T
   float scale_log2;        // d^-1/2 * log2(e)
   bf16* out;
@@ -120,7 +130,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     mbar_init(q_full, 1);
-    for (int s = 0; s < NST; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    for (int s = 0; s < NST; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 2); }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&s_full[s], 1);
       mbar_init(&p_full[s], 128 * TPR);
@@ -167,8 +177,8 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       __syncwarp();
       if (++st == NST) { st = 0; ph ^= 1; }
     }
-  } else if (warp == MW) {
-    // ===================== UMMA issuer =====================
+  } else if (warp == MW || warp == MW + 1) {
+    // ===================== UMMA issuers =====================
     const uint32_t idesc_s = umma_idesc((uint32_t)BN, false, 1u);
     const uint32_t idesc_o = umma_idesc((uint32_t)DP, true, 1u);
     const uint32_t sQ_a = smem_u32(sQ), sK_a = smem_u32(sK), sV_a = smem_u32(sV), sP_a = smem_u32(sP);
@@ -198,71 +208,34 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       }
       __syncwarp();
     };
+    // One issuer warp PER query tile (warp MW -> tile A, warp MW+1 -> tile B).  With a single in-order issuer the two
+    // tiles were coupled: S_A(j+1) could not be issued while the warp sat in its wait for P_B(j-1), so the tiles ran
+    // in lock-step, both in their MUFU-bound exponent phase at the same time (tools/fa_waits.py: exp 1890 cycles per
+    // key tile against 896 uncontended, 300-1000 cycles waiting for S).  Each issuer now only follows its own tile:
+    //   S_t(j+1) as soon as the softmax threads of tile t hold S_t(j) in registers, PV_t(j) when P_t(j) is in smem;
+    // a K/V ring stage is released by both (kv_empty counts two arrivals).
+    const int mt = warp - MW;
     mbar_wait(q_full, 0);
     mbar_wait(&kv_full[0], 0);
     tc_fence_after();
-    issue_s(0, 0);
-    issue_s(1, 0);
-    int st = 0, st_prev = 0;
+    issue_s(mt, 0);
+    int st = 0;
     uint32_t ph = 0;
     for (int j = 0; j < p.nkv; ++j) {
       int st_n = st + 1;
       uint32_t ph_n = ph;
       if (st_n == NST) { st_n = 0; ph_n ^= 1; }
-      const bool more = (j + 1 < p.nkv);
-      if (p.stagger) {
-        // Anti-phase schedule: tile B runs half a key tile behind tile A (its first exponent phase waits for A's), so
-        // that one tile's MUFU-bound exponent phase overlaps the other's max / pack / store phases instead of both
-        // contending for the 16 ex2 / clk / SM at the same time.  The issue order follows that timeline:
-        //   S_A(j+1), PV_B(j-1), S_B(j+1), PV_A(j)
-        if (more) {
-          mbar_wait(&kv_full[st_n], ph_n);
-          mbar_wait(&s_read[0], j & 1);
-          tc_fence_after();
-          issue_s(0, st_n);
-        }
-        if (j > 0) {
-          mbar_wait(&p_full[1], (j - 1) & 1);
-          tc_fence_after();
-          issue_pv(1, st_prev, j == 1, true);
-        }
-        if (more) {
-          mbar_wait(&s_read[1], j & 1);
-          tc_fence_after();
-          issue_s(1, st_n);
-        }
-        mbar_wait(&p_full[0], j & 1);
-        tc_fence_after();
-        issue_pv(0, st, j == 0, false);
-        st_prev = st;
-        st = st_n;
-        ph = ph_n;
-        continue;
-      }
-      if (more) {
-        // S_t(j+1) as soon as the softmax threads of tile t hold S_t(j) in registers: the next score tile is
-        // ready before they finish their exponentials
+      if (j + 1 < p.nkv) {
         mbar_wait(&kv_full[st_n], ph_n);
-        mbar_wait(&s_read[0], j & 1);
+        mbar_wait(&s_read[mt], j & 1);
         tc_fence_after();
-        issue_s(0, st_n);
-        mbar_wait(&s_read[1], j & 1);
-        tc_fence_after();
-        issue_s(1, st_n);
+        issue_s(mt, st_n);
       }
-      mbar_wait(&p_full[0], j & 1);
+      mbar_wait(&p_full[mt], j & 1);
       tc_fence_after();
-      issue_pv(0, st, j == 0, false);
-      mbar_wait(&p_full[1], j & 1);
-      tc_fence_after();
-      issue_pv(1, st, j == 0, true);
+      issue_pv(mt, st, j == 0, true);
       st = st_n;
       ph = ph_n;
-    }
-    if (p.stagger) {
-      mbar_wait(&p_full[1], (p.nkv - 1) & 1);
-      tc_fence_after();
-      issue_pv(1, st_prev, p.nkv == 1, true);
     }
   }
   } else {
@@ -283,15 +256,22 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const float sc = p.scale_log2;
     float m_used = -INFINITY;       // maximum (scaled, log2 units) the stored O / l are relative to
     float l = 0.f;
+    long long c_sfull = 0, c_ld = 0, c_max = 0, c_exp = 0, c_ofull = 0, c_store = 0;
+    const long long c_begin = fa_clock();
     for (int j = 0; j < p.nkv; ++j) {
+      const long long k0 = fa_clock();
       mbar_wait(&s_full[t], j & 1);
       tc_fence_after();
+      const long long k1 = fa_clock();
+      c_sfull += k1 - k0;
       float s[HC];
 #pragma unroll
       for (int c = 0; c < HC; c += 32) tmem_ld_32x32b_x32(s_tmem + c, reinterpret_cast<uint32_t*>(s + c));
       tmem_wait_ld();
       tc_fence_before();
       mbar_arrive(&s_read[t]);
+      const long long k2 = fa_clock();
+      c_ld += k2 - k1;
       const int kbase = j * BN + hf * HC;
       if (kbase + HC > p.Lk) {
 #pragma unroll
@@ -315,6 +295,8 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mx = fmaxf(mx, slot[(hf ^ 1) * 128 + row]);
       }
       mx *= sc;
+      const long long k3 = fa_clock();
+      c_max += k3 - k2;
       if (p.stagger && j == 0 && t == 1) mbar_wait(stag, 0);      // tile B starts its exponentials after tile A's
       // lazy rescale: keep the old reference maximum unless this row's maximum grew by more than 2^8
       const bool need = mx > m_used + 8.0f;
@@ -330,11 +312,15 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       }
       if (p.stagger && j == 0 && t == 0) mbar_arrive(stag);
       const float sum = ((sum8[0] + sum8[1]) + (sum8[2] + sum8[3])) + ((sum8[4] + sum8[5]) + (sum8[6] + sum8[7]));
+      const long long k4 = fa_clock();
+      c_exp += k4 - k3;
       // PV(j-1) must be complete before P is overwritten or O rescaled
       if (j > 0) {
         mbar_wait(&o_full[t], (j - 1) & 1);
         tc_fence_after();
       }
+      const long long k5 = fa_clock();
+      c_ofull += k5 - k4;
       if (__any_sync(0xffffffffu, need) && j > 0) {
         const float alpha = need ? fast_exp2(m_used - m_new) : 1.0f;
 #pragma unroll 1
@@ -365,6 +351,12 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(&p_full[t]);
+      c_store += fa_clock() - k5;
+    }
+    if (p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (warp == 0 || warp == 4 * TPR) && lane == 0) {
+      long long* d = p.dbg + (warp ? 8 : 0);
+      d[0] = fa_clock() - c_begin; d[1] = c_sfull; d[2] = c_ld; d[3] = c_max; d[4] = c_exp; d[5] = c_ofull;
+      d[6] = c_store; d[7] = p.nkv;
     }
     // ---- epilogue: O / l -> bf16 ----
     mbar_wait(&o_full[t], (p.nkv - 1) & 1);
@@ -438,6 +430,7 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   // without on the same box at L=4096 d=40, and 2.34 ms per layer inside the step -> off by default
   static const int stagger = getenv("B200AD_FA_STAGGER") ? atoi(getenv("B200AD_FA_STAGGER")) : 0;
   p.stagger = stagger;
+  p.dbg = g_fa_dbg;
   p.dk16 = (d + 15) / 16;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)d);
   p.out = reinterpret_cast<bf16*>(out);

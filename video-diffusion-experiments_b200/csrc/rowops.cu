@@ -5,77 +5,80 @@
 namespace b200ad {
 
 // ----------------------------------------------------------------------------- LayerNorm (+PE)
-// One warp per LN_ROWS rows, the rows live in registers (float2 per lane, lane-strided => coalesced 256 B requests).
-static constexpr int LN_ROWS = 1;   // 2 measured slower in the step (4.8 vs 3.4 ms over 111 launches): fewer warps in flight
+// Persistent warps: each warp walks rows warp, warp + nwarps, ... with the row in registers (float2 per lane,
+// lane-strided => coalesced 256 B requests) and the NEXT row's loads already in flight while the current row goes
+// through its two shuffle reductions and its stores.  (One short-lived warp per row reached 3.9-4.5 TB/s: a warp's
+// 1.3 KB of loads, two serial 5-step reductions and the block turn-over left the memory pipe idle in between.)
 template <typename T, int MAXP>   // MAXP = max float2 per lane  (C <= 64*MAXP)
-__global__ void layernorm_kernel(const float* __restrict__ x, int rows, int C, const float* __restrict__ gamma,
-                                 const float* __restrict__ beta, float eps, const float* __restrict__ pe, int hw,
-                                 int frames, T* __restrict__ out) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, int rows, int C,
+                                                        const float* __restrict__ gamma,
+                                                        const float* __restrict__ beta, float eps,
+                                                        const float* __restrict__ pe, int hw, int frames,
+                                                        T* __restrict__ out) {
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
   const int lane = threadIdx.x & 31;
-  const int row0 = warp * LN_ROWS;
-  if (row0 >= rows) return;
   const int npairs = C >> 1;
-  float2 v[LN_ROWS][MAXP];
-  float s[LN_ROWS];
-#pragma unroll
-  for (int r = 0; r < LN_ROWS; ++r) {
-    s[r] = 0.f;
-    const bool live = row0 + r < rows;
-    const float* xr = x + (long long)(row0 + (live ? r : 0)) * C;
+  const float inv_c = 1.0f / (float)C;
+  int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= rows) return;
+  constexpr bool CACHE_GB = MAXP <= 5;       // narrow rows keep gamma / beta in registers; wide rows re-read them (L1)
+  float2 g[CACHE_GB ? MAXP : 1], b[CACHE_GB ? MAXP : 1];
+  if (CACHE_GB) {
 #pragma unroll
     for (int j = 0; j < MAXP; ++j) {
       const int pr = lane + 32 * j;
-      if (pr < npairs) v[r][j] = *reinterpret_cast<const float2*>(xr + 2 * pr);
+      if (pr < npairs) {
+        g[j] = *reinterpret_cast<const float2*>(gamma + 2 * pr);
+        b[j] = *reinterpret_cast<const float2*>(beta + 2 * pr);
+      }
     }
   }
-#pragma unroll
-  for (int r = 0; r < LN_ROWS; ++r)
-#pragma unroll
-    for (int j = 0; j < MAXP; ++j)
-      if (lane + 32 * j < npairs) s[r] += v[r][j].x + v[r][j].y;
-  float mean[LN_ROWS], q[LN_ROWS], rstd[LN_ROWS];
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-    for (int r = 0; r < LN_ROWS; ++r) s[r] += __shfl_xor_sync(0xffffffffu, s[r], o);
-#pragma unroll
-  for (int r = 0; r < LN_ROWS; ++r) {
-    mean[r] = s[r] / (float)C;
-    q[r] = 0.f;
-#pragma unroll
-    for (int j = 0; j < MAXP; ++j)
-      if (lane + 32 * j < npairs) {
-        const float a = v[r][j].x - mean[r], b = v[r][j].y - mean[r];
-        q[r] += a * a + b * b;
-      }
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-    for (int r = 0; r < LN_ROWS; ++r) q[r] += __shfl_xor_sync(0xffffffffu, q[r], o);
-#pragma unroll
-  for (int r = 0; r < LN_ROWS; ++r) rstd[r] = rsqrtf(q[r] / (float)C + eps);
-  const float* per[LN_ROWS];
-#pragma unroll
-  for (int r = 0; r < LN_ROWS; ++r)
-    per[r] = pe ? pe + (long long)((int)((row0 + r) / hw) % frames) * C : nullptr;
+  float2 nxt[MAXP];
 #pragma unroll
   for (int j = 0; j < MAXP; ++j) {
     const int pr = lane + 32 * j;
-    if (pr < npairs) {
-      const float2 g = *reinterpret_cast<const float2*>(gamma + 2 * pr);
-      const float2 b = *reinterpret_cast<const float2*>(beta + 2 * pr);
+    if (pr < npairs) nxt[j] = *reinterpret_cast<const float2*>(x + (long long)row * C + 2 * pr);
+  }
+  for (; row < rows; row += nwarps) {
+    float2 v[MAXP];
+    float s = 0.f;
 #pragma unroll
-      for (int r = 0; r < LN_ROWS; ++r) {
-        if (row0 + r >= rows) break;
-        float a0 = (v[r][j].x - mean[r]) * rstd[r] * g.x + b.x;
-        float a1 = (v[r][j].y - mean[r]) * rstd[r] * g.y + b.y;
-        if (per[r]) {
-          const float2 p2 = *reinterpret_cast<const float2*>(per[r] + 2 * pr);
+    for (int j = 0; j < MAXP; ++j) {
+      v[j] = nxt[j];
+      if (lane + 32 * j < npairs) s += v[j].x + v[j].y;
+    }
+    const int row_n = row + nwarps;
+    if (row_n < rows) {
+#pragma unroll
+      for (int j = 0; j < MAXP; ++j) {
+        const int pr = lane + 32 * j;
+        if (pr < npairs) nxt[j] = *reinterpret_cast<const float2*>(x + (long long)row_n * C + 2 * pr);
+      }
+    }
+    const float mean = warp_sum(s) * inv_c;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXP; ++j)
+      if (lane + 32 * j < npairs) {
+        const float a0 = v[j].x - mean, a1 = v[j].y - mean;
+        q += a0 * a0 + a1 * a1;
+      }
+    const float rstd = rsqrtf(warp_sum(q) * inv_c + eps);
+    const float* per = pe ? pe + (long long)((row / hw) % frames) * C : nullptr;
+    T* orow = out + (long long)row * C;
+#pragma unroll
+    for (int j = 0; j < MAXP; ++j) {
+      const int pr = lane + 32 * j;
+      if (pr < npairs) {
+        const float2 gj = CACHE_GB ? g[CACHE_GB ? j : 0] : *reinterpret_cast<const float2*>(gamma + 2 * pr);
+        const float2 bj = CACHE_GB ? b[CACHE_GB ? j : 0] : *reinterpret_cast<const float2*>(beta + 2 * pr);
+        float a0 = (v[j].x - mean) * rstd * gj.x + bj.x;
+        float a1 = (v[j].y - mean) * rstd * gj.y + bj.y;
+        if (per) {
+          const float2 p2 = *reinterpret_cast<const float2*>(per + 2 * pr);
           a0 += p2.x; a1 += p2.y;
         }
-        store2<T>(out + (long long)(row0 + r) * C + 2 * pr, a0, a1);
+        store2<T>(orow + 2 * pr, a0, a1);
       }
     }
   }
@@ -186,8 +189,16 @@ extern "C" int b200ad_layernorm(int op_dtype, const float* x, int rows, int C, c
   B200AD_REQUIRE(C % 2 == 0 && C <= 64 * 20, "layernorm: C=%d unsupported (even, <= 1280)", C);
   if (!pe) { hw = 1; frames = 1; }
   const int threads = 256;
-  const long long nwarps = ((long long)rows + LN_ROWS - 1) / LN_ROWS;
-  const int blocks = (int)((nwarps * 32 + threads - 1) / threads);
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    B200AD_CHECK_CUDA(cudaGetDevice(&dev));
+    B200AD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  // persistent: at most one wave of blocks (8 per SM at <= 64 registers, fewer for the wide rows)
+  const long long want = ((long long)rows * 32 + threads - 1) / threads;
+  const int per_sm = C <= 320 ? 8 : (C <= 640 ? 3 : 2);      // resident blocks at 64 / 80 / 128 registers
+  const int blocks = (int)(want < (long long)sms * per_sm ? want : (long long)sms * per_sm);
   cudaStream_t st = (cudaStream_t)stream;
 #define LN_LAUNCH(TT, MP) \
   layernorm_kernel<TT, MP><<<blocks, threads, 0, st>>>(x, rows, C, gamma, beta, eps, pe, hw, frames, (TT*)out_op)
