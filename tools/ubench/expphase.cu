@@ -7,8 +7,8 @@
 
 __device__ __forceinline__ float ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-template <bool SUM>
-__global__ void __launch_bounds__(512) k(float* out, float sc, float m, int iters, long long* cyc) {
+template <bool SUM, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1) k(float* out, float sc, float m, int iters, long long* cyc) {
   float s[128];
 #pragma unroll
   for (int i = 0; i < 128; ++i) s[i] = (float)((threadIdx.x * 131 + i * 17) & 255) * -0.01f;
@@ -41,16 +41,15 @@ int main() {
   float* out; cudaMalloc(&out, p.multiProcessorCount * 512 * 4);
   long long* cyc; cudaMallocManaged(&cyc, 8);
   const int iters = 200;
-  for (int warps_per_smsp = 1; warps_per_smsp <= 4; warps_per_smsp *= 2) {
-    const int threads = 128 * warps_per_smsp;
-    for (int sum = 0; sum < 2; ++sum) {
-      if (sum) k<true><<<p.multiProcessorCount, threads>>>(out, 0.9f, -0.3f, iters, cyc);
-      else k<false><<<p.multiProcessorCount, threads>>>(out, 0.9f, -0.3f, iters, cyc);
-      cudaDeviceSynchronize();
-      printf("%d warp(s) per SM sub-partition, row sum %s: %.0f cycles per 128-element row phase (incl. 128 FMUL feedback)\n",
-             warps_per_smsp, sum ? "on " : "off", (double)*cyc / iters);
-    }
+#define RUN(W)                                                                                                   \
+  for (int sum = 0; sum < 2; ++sum) {                                                                            \
+    if (sum) k<true, 128 * W><<<p.multiProcessorCount, 128 * W>>>(out, 0.9f, -0.3f, iters, cyc);                  \
+    else k<false, 128 * W><<<p.multiProcessorCount, 128 * W>>>(out, 0.9f, -0.3f, iters, cyc);                     \
+    cudaDeviceSynchronize();                                                                                     \
+    printf("%d warp(s) per SM sub-partition, row sum %s: %.0f cycles per 128-element row phase (incl. 128 FMUL feedback)\n", \
+           W, sum ? "on " : "off", (double)*cyc / iters);                                                        \
   }
+  RUN(1) RUN(2) RUN(3)
   printf("status: %s\n", cudaGetErrorString(cudaDeviceSynchronize()));
   return 0;
 }

@@ -3,11 +3,12 @@
 //   O = softmax(Q K^T / sqrt(d)) V per (frame-image n, head); bf16 operands, fp32 S / O accumulators in TMEM.
 // One CTA owns TWO query tiles of 128 rows (A and B) of one (n, head) and walks the keys in tiles of BN:
 //   warps 0..3  softmax of tile A, warps 4..7 softmax of tile B: one thread per query row; the whole score row is
-//               held in registers (tcgen05.ld), exp2 with the running maximum, bf16 P written to swizzled smem
+//               held in registers (tcgen05.ld), exp2 with the running maximum, bf16 P written to TENSOR MEMORY
+//               (tcgen05.st; the PV MMA takes its A operand from there) -- or to swizzled smem (PT = false)
 //   warp 8      TMA producer: Q_A, Q_B once, then K_j / V_j through a ring of NST stages
-//   warp 9      UMMA issuer:  S_A(j)=Q_A K_j^T, S_B(j)=Q_B K_j^T, O_A+=P_A(j)V_j, O_B+=P_B(j)V_j; S_t(j+1) is issued as
-//               soon as the softmax threads of tile t hold S_t(j) in registers
-//   warps 10,11 idle (they complete the third warpgroup so that setmaxnreg can move registers: the softmax
+//   warps 9,10  UMMA issuers, one per query tile t: S_t(j)=Q_t K_j^T, O_t+=P_t(j)V_j; S_t(j+1) is issued as soon as
+//               the softmax threads of tile t hold S_t(j) in registers
+//   warp 11     idle (completes the third warpgroup so that setmaxnreg can move registers: the softmax
 //               warpgroups run with 232 registers per thread, the third one with 40)
 // The layers this kernel serves are bound by the exponential (128 x 128 exp2 per 2.6 MFLOP of useful MMA at d=40),
 // so the structure aims at keeping both softmax groups busy all the time:
@@ -21,6 +22,7 @@ namespace b200ad {
 
 // threads per CTA: 8*TPR softmax warps + one warpgroup holding the TMA producer, the UMMA issuer and two idle warps
 __host__ __device__ constexpr int fa_threads(int tpr) { return (8 * tpr + 4) * 32; }
+__host__ __device__ constexpr int fa_nst(int tpr, bool pt) { return pt ? 5 : (tpr == 1 ? 4 : 3); }
 
 // Cycle counters of the softmax loop for tools/fa_waits.py (compiled in with -DB200AD_GEMM_PROFILE only).
 #ifdef B200AD_GEMM_PROFILE
@@ -89,18 +91,26 @@ __device__ __forceinline__ uint32_t pack_p(float lo, float hi) {
 // row's columns (16 softmax warps, four per scheduler, 104 registers each); they exchange the row maximum through
 // shared memory once per key tile (double-buffered by tile parity, one named barrier per query tile) and split the O
 // columns of the lazy rescale and of the final normalisation.
-template <int DP, int BN, bool VS, int TPR>
+// PT: the bf16 probabilities go to TENSOR MEMORY (tcgen05.st, two per 32-bit column) and the PV MMA reads its A operand
+// from there.  Per key tile and query tile that removes 32 KB of st.shared and 32 KB of operand reads from a shared
+// memory pipe that otherwise moves 256 KB per key tile (K/V fill 32, Q+K reads 64, P writes 64, P+V reads 96) --
+// 2048 cycles at 128 B/clk, as much as the MUFU floor of the exponentials.  The freed 64 KB deepen the K/V ring.
+template <int DP, int BN, bool VS, int TPR, bool PT>
 __global__ void __launch_bounds__(fa_threads(TPR), 1)
 attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ FaParams p) {
   constexpr int NS = DP / 64;                    // 64-column slabs per operand row
-  constexpr int NST = 3;                         // K/V ring depth
+  // K/V ring depth.  Four stages (everything the 227 KB allow) when one thread owns a row: with three, a K/V tile is
+  // requested only ~1.4 key tiles before its S MMA, which pulls the two query tiles back into lock-step whenever one
+  // runs half a tile behind the other (the anti-phase schedule needs that slack).
+  constexpr int NST = fa_nst(TPR, PT);
   constexpr int QSLAB = 128 * 128;               // [128 rows x 64 bf16]
   constexpr int KSLAB = BN * 128;                // [BN rows x 64 bf16]
   constexpr int PS = BN / 64;                    // P slabs (each [128 q rows x 64 keys])
   constexpr uint32_t S_COL0 = 0, S_COL1 = BN, O_COL0 = 2 * BN, O_COL1 = 2 * BN + DP;
+  constexpr uint32_t P_COL0 = 2 * BN + 2 * DP, P_COL1 = P_COL0 + BN / 2;     // PT: [128 lanes x BN/2 columns] bf16x2
   constexpr uint32_t TMEM_COLS = 512;
-  static_assert(2 * BN + 2 * DP <= 512, "TMEM budget");
+  static_assert(2 * BN + 2 * DP + (PT ? BN : 0) <= 512, "TMEM budget");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -108,7 +118,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   uint8_t* sK = sQ + 2 * NS * QSLAB;                   // [NST][NS]
   uint8_t* sV = sK + NST * NS * KSLAB;                 // [NST][NS]
   uint8_t* sP = sV + NST * NS * KSLAB;                 // [2][PS]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * PS * QSLAB);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + (PT ? 0 : 2 * PS * QSLAB));
   uint64_t* q_full = bars;                             // [1]
   uint64_t* kv_full = bars + 1;                        // [NST]
   uint64_t* kv_empty = kv_full + NST;                  // [NST]
@@ -199,9 +209,14 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < BN / 16; ++kk) {
-          const uint64_t adesc = umma_desc_k_sw128(sP_a + (uint32_t)((t * PS + (kk >> 2)) * QSLAB)) + (uint64_t)(2 * (kk & 3));
           const uint64_t bdesc = umma_desc_mn_sw128(sV_a + (uint32_t)(st * NS * KSLAB + kk * 2048), (uint32_t)KSLAB);
-          umma_f16_ss(tmem_base + (t ? O_COL1 : O_COL0), adesc, bdesc, idesc_o, (first && kk == 0) ? 0u : 1u);
+          if (PT) {
+            umma_f16_ts(tmem_base + (t ? O_COL1 : O_COL0), tmem_base + (t ? P_COL1 : P_COL0) + (uint32_t)(kk * 8), bdesc,
+                        idesc_o, (first && kk == 0) ? 0u : 1u);
+          } else {
+            const uint64_t adesc = umma_desc_k_sw128(sP_a + (uint32_t)((t * PS + (kk >> 2)) * QSLAB)) + (uint64_t)(2 * (kk & 3));
+            umma_f16_ss(tmem_base + (t ? O_COL1 : O_COL0), adesc, bdesc, idesc_o, (first && kk == 0) ? 0u : 1u);
+          }
         }
         umma_commit(&o_full[t]);
         if (release_kv) umma_commit(&kv_empty[st]);
@@ -251,6 +266,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
     const uint32_t s_tmem = tmem_base + lane_addr + (t ? S_COL1 : S_COL0) + (uint32_t)(hf * HC);
     const uint32_t o_tmem = tmem_base + lane_addr + (t ? O_COL1 : O_COL0);
+    const uint32_t p_tmem = tmem_base + lane_addr + (t ? P_COL1 : P_COL0) + (uint32_t)(hf * (HC / 2));
     const uint32_t p_row = smem_u32(sP + t * PS * QSLAB) + (uint32_t)(row * 128);
     const int sw = row & 7;
     const float sc = p.scale_log2;
@@ -337,6 +353,15 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       }
       m_used = m_new;
       l += sum;
+      if (PT) {
+        // bf16 P row -> this thread's TMEM lane, two keys per column
+        uint32_t pk[HC / 2];
+#pragma unroll
+        for (int i = 0; i < HC / 2; ++i) pk[i] = pack_p<VS>(s[2 * i], s[2 * i + 1]);
+#pragma unroll
+        for (int c = 0; c < HC / 2; c += 32) tmem_st_32x32b_x32(p_tmem + c, pk + c);
+        tmem_wait_st();
+      } else {
       // bf16 P row -> swizzled smem: 8 keys per 16-byte chunk, chunk index XOR (row & 7) inside each 64-key slab
 #pragma unroll
       for (int c8 = 0; c8 < HC / 8; ++c8) {
@@ -349,6 +374,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                      : "memory");
       }
       fence_proxy_async_smem();
+      }
       tc_fence_before();
       mbar_arrive(&p_full[t]);
       c_store += fa_clock() - k5;
@@ -405,7 +431,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   }
 }
 
-template <int DP, int BN, bool VS, int TPR>
+template <int DP, int BN, bool VS, int TPR, bool PT>
 static int launch_attn_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                           int nbatch, int heads, int L, int d, void* out, long long ldo, cudaStream_t stream) {
   constexpr int NS = DP / 64;
@@ -426,9 +452,10 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   FaParams p;
   p.Lq = L; p.Lk = L; p.d = d;
   p.nkv = (L + BN - 1) / BN;
-  // measured (profiles/kbench_attention_variants_r01.txt): 1.82-2.08 ms with the anti-phase schedule vs 1.99-2.04 ms
-  // without on the same box at L=4096 d=40, and 2.34 ms per layer inside the step -> off by default
-  static const int stagger = getenv("B200AD_FA_STAGGER") ? atoi(getenv("B200AD_FA_STAGGER")) : 0;
+  // measured (profiles/kbench_attention_variants_r01.txt, L=4096 d=40, V ones column): with one issuer warp per query
+  // tile, P in tensor memory and a 5-stage K/V ring the anti-phase start gives 1.62 ms against 1.71 ms without
+  // (it was a loss with the single in-order issuer) -> on by default
+  static const int stagger = getenv("B200AD_FA_STAGGER") ? atoi(getenv("B200AD_FA_STAGGER")) : 1;
   p.stagger = stagger;
   p.dbg = g_fa_dbg;
   p.dk16 = (d + 15) / 16;
@@ -436,14 +463,16 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   p.out = reinterpret_cast<bf16*>(out);
   p.ldo = ldo;
   // slabs + alignment + barriers + row-maximum exchange of the two-threads-per-row variant
-  const size_t smem = (size_t)(2 * NS * 128 * 128 + 2 * 3 * NS * BN * 128 + 2 * (BN / 64) * 128 * 128) + 1024 + 256 + 4096;
+  const size_t smem = (size_t)(2 * NS * 128 * 128 + 2 * fa_nst(TPR, PT) * NS * BN * 128 + (PT ? 0 : 2 * (BN / 64) * 128 * 128)) +
+                      1024 + 256 + (TPR == 2 ? 4096 : 0);
+  B200AD_REQUIRE(smem <= 232448, "attention: %zu bytes of shared memory", smem);
   static bool attr = false;
   if (!attr) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN, VS, TPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN, VS, TPR, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr = true;
   }
   dim3 grid(L / 256, heads, nbatch);
-  attn_fa_kernel<DP, BN, VS, TPR><<<grid, fa_threads(TPR), smem, stream>>>(tmQ, tmK, tmV, p);
+  attn_fa_kernel<DP, BN, VS, TPR, PT><<<grid, fa_threads(TPR), smem, stream>>>(tmQ, tmK, tmV, p);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -458,13 +487,18 @@ int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk
   // A/B switch for kbench.  Two threads per row measured no faster than one (1.91 vs 1.87 ms at L=4096 d=40): the
   // loop is not latency-bound, so the simpler variant stays the default.
   static const int tpr = getenv("B200AD_FA_TPR") ? atoi(getenv("B200AD_FA_TPR")) : 1;
+  // P in tensor memory (tcgen05.st + A-from-TMEM PV MMA): 1.71 vs 1.87 ms at L=4096 d=40, 223 vs 229 us at L=1024 d=80
+  static const int pt = getenv("B200AD_FA_PT") ? atoi(getenv("B200AD_FA_PT")) : 1;
 #define FA_LAUNCH(DPV, BNV)                                                                                         \
   do {                                                                                                              \
+    if (tpr == 1 && pt)                                                                                             \
+      return vs ? launch_attn_fa<DPV, BNV, true, 1, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)  \
+                : launch_attn_fa<DPV, BNV, false, 1, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream); \
     if (tpr == 1)                                                                                                   \
-      return vs ? launch_attn_fa<DPV, BNV, true, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)  \
-                : launch_attn_fa<DPV, BNV, false, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream); \
-    return vs ? launch_attn_fa<DPV, BNV, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)    \
-              : launch_attn_fa<DPV, BNV, false, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);  \
+      return vs ? launch_attn_fa<DPV, BNV, true, 1, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)  \
+                : launch_attn_fa<DPV, BNV, false, 1, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream); \
+    return vs ? launch_attn_fa<DPV, BNV, true, 2, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)    \
+              : launch_attn_fa<DPV, BNV, false, 2, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);  \
   } while (0)
   if (dpad == 64) FA_LAUNCH(64, 128);
   if (dpad == 128) FA_LAUNCH(128, 64);
