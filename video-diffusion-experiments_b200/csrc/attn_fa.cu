@@ -77,6 +77,10 @@ __device__ __forceinline__ uint32_t pack_p(float lo, float hi) {
   }
   return pack_bf16x2(lo, hi);
 }
+#ifndef B200AD_FA_SPEC
+#define B200AD_FA_SPEC 0           // speculative exponentials against the previous reference maximum (see the softmax loop):
+                                   // measured SLOWER (1.77 vs 1.62 ms at L=4096 d=40: the fused loop schedules worse) -> opt-in
+#endif
 #ifndef B200AD_FA_EMU_EVERY
 #define B200AD_FA_EMU_EVERY 8      // every 8th exponential runs on the FMA pipes instead of the MUFU unit
 #endif
@@ -259,6 +263,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");   // 512*104 + 128*40 <= 640*96 (the CTA's own allocation)
     constexpr int HC = BN / TPR;                 // score columns per thread
     constexpr int OC = DP / TPR;                 // O columns per thread (rescale, normalisation)
+    constexpr bool SPEC = PT && TPR == 1 && B200AD_FA_SPEC;
     const int t = warp / (4 * TPR);
     const int hf = (warp >> 2) % TPR;            // which part of the row's columns
     const int quarter = warp & 3;
@@ -294,6 +299,47 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int i = 0; i < HC; ++i)
           if (kbase + i >= p.Lk) s[i] = -INFINITY;
       }
+      long long k3 = k2;
+      uint32_t pk[PT ? HC / 2 : 1];                // PT: the packed bf16 probabilities of this row
+      bool need;
+      float m_new;
+      float sum8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      auto exp_one = [&](int i, float x) {
+        return (B200AD_FA_EMU_EVERY > 0 && (i % B200AD_FA_EMU_EVERY) == B200AD_FA_EMU_EVERY - 1) ? poly_exp2(x) : fast_exp2(x);
+      };
+      if (SPEC) {
+        // Speculate that the reference maximum stays (true for all but the first few key tiles with the 2^8 slack of
+        // the lazy rescale): exponentials against the OLD maximum, packed at once, with the row maximum computed in
+        // the shadow of the MUFU pipe instead of in a phase of its own.  The scores stay in registers; a row whose
+        // maximum did grow past the slack recomputes from them below -- same values as the non-speculative order.
+        if (p.stagger && j == 0 && t == 1) mbar_wait(stag, 0);
+        const float neg_old = -m_used;
+        float mx8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) mx8[i] = s[i];
+#pragma unroll
+        for (int i = 0; i < HC; i += 2) {
+          const float e0 = exp_one(i, fmaf(s[i], sc, neg_old)), e1 = exp_one(i + 1, fmaf(s[i + 1], sc, neg_old));
+          pk[i / 2] = pack_p<VS>(e0, e1);
+          if (!VS) { sum8[i & 7] += e0; sum8[(i + 1) & 7] += e1; }
+          if (i >= 8) { mx8[i & 7] = fmaxf(mx8[i & 7], s[i]); mx8[(i + 1) & 7] = fmaxf(mx8[(i + 1) & 7], s[i + 1]); }
+        }
+        const float mx = sc * fmaxf(fmaxf(fmaxf(mx8[0], mx8[1]), fmaxf(mx8[2], mx8[3])),
+                                    fmaxf(fmaxf(mx8[4], mx8[5]), fmaxf(mx8[6], mx8[7])));
+        need = mx > m_used + 8.0f;
+        m_new = need ? mx : m_used;
+        if (need) {
+          const float neg_m = -m_new;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) sum8[i] = 0.f;
+#pragma unroll
+          for (int i = 0; i < HC; i += 2) {
+            const float e0 = exp_one(i, fmaf(s[i], sc, neg_m)), e1 = exp_one(i + 1, fmaf(s[i + 1], sc, neg_m));
+            pk[i / 2] = pack_p<VS>(e0, e1);
+            if (!VS) { sum8[i & 7] += e0; sum8[(i + 1) & 7] += e1; }
+          }
+        }
+      } else {
       // 8 independent chains: a single max / sum chain is HC dependent 4-cycle ops per row
       float mx8[8];
 #pragma unroll
@@ -311,20 +357,22 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mx = fmaxf(mx, slot[(hf ^ 1) * 128 + row]);
       }
       mx *= sc;
-      const long long k3 = fa_clock();
+      k3 = fa_clock();
       c_max += k3 - k2;
       if (p.stagger && j == 0 && t == 1) mbar_wait(stag, 0);      // tile B starts its exponentials after tile A's
       // lazy rescale: keep the old reference maximum unless this row's maximum grew by more than 2^8
-      const bool need = mx > m_used + 8.0f;
-      const float m_new = need ? mx : m_used;
+      need = mx > m_used + 8.0f;
+      m_new = need ? mx : m_used;
       const float neg_m = -m_new;
-      float sum8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int i = 0; i < HC; ++i) {
-        const float x = fmaf(s[i], sc, neg_m);
-        s[i] = (B200AD_FA_EMU_EVERY > 0 && (i % B200AD_FA_EMU_EVERY) == B200AD_FA_EMU_EVERY - 1) ? poly_exp2(x)
-                                                                                             : fast_exp2(x);
+        s[i] = exp_one(i, fmaf(s[i], sc, neg_m));
         if (!VS) sum8[i & 7] += s[i];
+      }
+      if (PT) {
+#pragma unroll
+        for (int i = 0; i < HC / 2; ++i) pk[i] = pack_p<VS>(s[2 * i], s[2 * i + 1]);
+      }
       }
       if (p.stagger && j == 0 && t == 0) mbar_arrive(stag);
       const float sum = ((sum8[0] + sum8[1]) + (sum8[2] + sum8[3])) + ((sum8[4] + sum8[5]) + (sum8[6] + sum8[7]));
@@ -355,9 +403,6 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       l += sum;
       if (PT) {
         // bf16 P row -> this thread's TMEM lane, two keys per column
-        uint32_t pk[HC / 2];
-#pragma unroll
-        for (int i = 0; i < HC / 2; ++i) pk[i] = pack_p<VS>(s[2 * i], s[2 * i + 1]);
 #pragma unroll
         for (int c = 0; c < HC / 2; c += 32) tmem_st_32x32b_x32(p_tmem + c, pk + c);
         tmem_wait_st();
