@@ -28,3 +28,10 @@ for (Ln, d, dp) in [(4096, 40, 64), (1024, 80, 128)]:
             print(f"L={Ln} d={d} v_ones={vs} {e0.elapsed_time(e1)*1e3:.0f} us | {name}: {v[0]/n:.0f} cycles per key tile = "
                   f"wait S {v[1]/n:.0f} + tcgen05.ld {v[2]/n:.0f} + max {v[3]/n:.0f} + exp {v[4]/n:.0f} + wait PV(j-1) {v[5]/n:.0f} "
                   f"+ rescale/pack/store {v[6]/n:.0f}", flush=True)
+        tl = dbg[64:64 + 48].cpu().tolist()
+        t0 = min(x for x in tl if x > 0) if any(x > 0 for x in tl) else 0
+        for t in range(3):
+            row = tl[t * 16:(t + 1) * 16]
+            if any(row):
+                print(f"    exp phases of key tiles 8..15, query tile {'ABC'[t]} (cycles from the first): " +
+                      " ".join(f"[{row[2*i]-t0}-{row[2*i+1]-t0}]" for i in range(8)), flush=True)

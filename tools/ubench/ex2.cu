@@ -53,7 +53,7 @@ __global__ void k(uint32_t* out, float seed) {
   }
   uint32_t acc = 0;
 #pragma unroll
-  for (int i = 0; i < ILP; ++i) acc ^= h[i] ^ __float_as_uint(x[i]);
+  for (int i = 0; i < ILP; ++i) acc = (acc * 31u + h[i]) * 31u + __float_as_uint(x[i]);   // (an XOR would cancel h against x in the pack modes)
   out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
 

@@ -21,8 +21,8 @@
 namespace b200ad {
 
 // threads per CTA: 8*TPR softmax warps + one warpgroup holding the TMA producer, the UMMA issuer and two idle warps
-__host__ __device__ constexpr int fa_threads(int tpr) { return (8 * tpr + 4) * 32; }
-__host__ __device__ constexpr int fa_nst(int tpr, bool pt) { return pt ? 5 : (tpr == 1 ? 4 : 3); }
+__host__ __device__ constexpr int fa_threads(int tpr, int nt = 2) { return (4 * nt * tpr + 4) * 32; }
+__host__ __device__ constexpr int fa_nst(int tpr, bool pt, int nt = 2) { return nt == 3 ? 6 : pt ? 5 : (tpr == 1 ? 4 : 3); }
 
 // Cycle counters of the softmax loop for tools/fa_waits.py (compiled in with -DB200AD_GEMM_PROFILE only).
 #ifdef B200AD_GEMM_PROFILE
@@ -61,18 +61,21 @@ __device__ __forceinline__ float poly_exp2(float x) {
   r = fmaf(r, f, 1.0f);
   return __int_as_float(__float_as_int(r) + (__float_as_int(j) << 23));
 }
-// Probabilities -> bf16 pair.  With the V-ones-column denominator (VS) numerator and denominator are sums of the SAME
-// bf16 values, so a truncating pack (one PRMT on the ALU pipe instead of F2FP) only shifts every P by the same
-// relative bias, which the normalisation cancels; the remaining rounding noise has the variance of round-to-nearest.
-// Opt-in (-DB200AD_FA_TRUNC_P=1) until measured.
+// Probabilities -> bf16 pair.  Default: F2FP (cvt.rn.bf16x2.f32).  Opt-in (-DB200AD_FA_TRUNC_P=1): pack on the ALU pipe --
+//   VS  (denominator from the V ones column): TRUNCATE with one PRMT; numerator and denominator are sums of the SAME
+//       bf16 values, so the common relative bias of truncation cancels in the normalisation;
+//   !VS: round half up (add 0x8000 to the bit patterns of the positive finite P), then the same PRMT.
+// Tested on the suspicion that F2FP shares the 16-lane XU pipe with MUFU.EX2: it does not bound the loop -- 1.560 ms
+// (PRMT) vs 1.548 ms (F2FP) at L=4096 d=40 with three query tiles -- so the exact rounding stays.
 #ifndef B200AD_FA_TRUNC_P
 #define B200AD_FA_TRUNC_P 0
 #endif
 template <bool VS>
 __device__ __forceinline__ uint32_t pack_p(float lo, float hi) {
-  if (VS && B200AD_FA_TRUNC_P) {
-    uint32_t r;
-    asm("prmt.b32 %0, %1, %2, 0x7632;" : "=r"(r) : "r"(__float_as_uint(lo)), "r"(__float_as_uint(hi)));
+  if (B200AD_FA_TRUNC_P) {
+    uint32_t a = __float_as_uint(lo), b = __float_as_uint(hi), r;
+    if (!VS) { a += 0x8000u; b += 0x8000u; }
+    asm("prmt.b32 %0, %1, %2, 0x7632;" : "=r"(r) : "r"(a), "r"(b));
     return r;
   }
   return pack_bf16x2(lo, hi);
@@ -99,41 +102,52 @@ __device__ __forceinline__ uint32_t pack_p(float lo, float hi) {
 // from there.  Per key tile and query tile that removes 32 KB of st.shared and 32 KB of operand reads from a shared
 // memory pipe that otherwise moves 256 KB per key tile (K/V fill 32, Q+K reads 64, P writes 64, P+V reads 96) --
 // 2048 cycles at 128 B/clk, as much as the MUFU floor of the exponentials.  The freed 64 KB deepen the K/V ring.
-template <int DP, int BN, bool VS, int TPR, bool PT>
-__global__ void __launch_bounds__(fa_threads(TPR), 1)
+// NT: query tiles per CTA.  With two, each scheduler hosts two softmax warps and a warp's chain per key tile (S wait,
+// tcgen05.ld, max, exp, pack, tcgen05.st: ~2400 cycles uncontended at BN = 128) is longer than the 2 x 896 cycles of
+// MUFU work the scheduler has per key tile, so the MUFU pipe idles a third of the time however the tiles are phased.
+// Three tiles (BN = 64 so that 3 x (S 64 + O 64 + P 32) = 480 TMEM columns fit; 16 warps, 128 registers each, no
+// setmaxnreg) put three softmax warps on every scheduler: the chain of one is covered by the exponentials of the
+// other two.
+template <int DP, int BN, bool VS, int TPR, bool PT, int NT>
+__global__ void __launch_bounds__(fa_threads(TPR, NT), 1)
 attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ FaParams p) {
   constexpr int NS = DP / 64;                    // 64-column slabs per operand row
   // K/V ring depth.  Four stages (everything the 227 KB allow) when one thread owns a row: with three, a K/V tile is
   // requested only ~1.4 key tiles before its S MMA, which pulls the two query tiles back into lock-step whenever one
   // runs half a tile behind the other (the anti-phase schedule needs that slack).
-  constexpr int NST = fa_nst(TPR, PT);
+  constexpr int NST = fa_nst(TPR, PT, NT);
   constexpr int QSLAB = 128 * 128;               // [128 rows x 64 bf16]
   constexpr int KSLAB = BN * 128;                // [BN rows x 64 bf16]
   constexpr int PS = BN / 64;                    // P slabs (each [128 q rows x 64 keys])
-  constexpr uint32_t S_COL0 = 0, S_COL1 = BN, O_COL0 = 2 * BN, O_COL1 = 2 * BN + DP;
-  constexpr uint32_t P_COL0 = 2 * BN + 2 * DP, P_COL1 = P_COL0 + BN / 2;     // PT: [128 lanes x BN/2 columns] bf16x2
+  // TMEM columns: S_t at t*BN, O_t behind the S tiles, P_t (PT: [128 lanes x BN/2 columns] bf16x2) behind the O tiles
+  auto S_COL = [](int t) { return (uint32_t)(t * BN); };
+  auto O_COL = [](int t) { return (uint32_t)(NT * BN + t * DP); };
+  auto P_COL = [](int t) { return (uint32_t)(NT * (BN + DP) + t * (BN / 2)); };
+  static_assert(NT == 2 || (NT == 3 && PT && TPR == 1), "three query tiles need P in tensor memory");
   constexpr uint32_t TMEM_COLS = 512;
-  static_assert(2 * BN + 2 * DP + (PT ? BN : 0) <= 512, "TMEM budget");
+  static_assert(NT * (BN + DP) + (PT ? NT * BN / 2 : 0) <= 512, "TMEM budget");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem;                                  // [2][NS] slabs
-  uint8_t* sK = sQ + 2 * NS * QSLAB;                   // [NST][NS]
+  uint8_t* sQ = smem;                                  // [NT][NS] slabs
+  uint8_t* sK = sQ + NT * NS * QSLAB;                   // [NST][NS]
   uint8_t* sV = sK + NST * NS * KSLAB;                 // [NST][NS]
   uint8_t* sP = sV + NST * NS * KSLAB;                 // [2][PS]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sP + (PT ? 0 : 2 * PS * QSLAB));
   uint64_t* q_full = bars;                             // [1]
   uint64_t* kv_full = bars + 1;                        // [NST]
   uint64_t* kv_empty = kv_full + NST;                  // [NST]
-  uint64_t* s_full = kv_empty + NST;                   // [2]
-  uint64_t* p_full = s_full + 2;                       // [2]  128 arrivals
-  uint64_t* o_full = p_full + 2;                       // [2]
-  uint64_t* s_read = o_full + 2;                       // [2]  128 arrivals: the S tile is in registers
-  uint64_t* stag = s_read + 2;                         // [1]  tile A's first exponent phase is over (stagger)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stag + 1);
-  float* smx = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2 parities][2 tiles][TPR][128]
-  constexpr int PW = 8 * TPR, MW = 8 * TPR + 1;        // producer / UMMA-issuer warp
+  uint64_t* s_full = kv_empty + NST;                   // [NT]
+  uint64_t* p_full = s_full + NT;                      // [NT]  128 arrivals
+  uint64_t* o_full = p_full + NT;                      // [NT]
+  uint64_t* s_read = o_full + NT;                      // [NT]  128 arrivals: the S tile is in registers
+  uint64_t* stag = s_read + NT;                        // [NT] tile t's first exponent phase is over (stagger)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stag + NT);
+  uint64_t* tok = reinterpret_cast<uint64_t*>(tmem_slot + 2);   // [NT][4] exponent-phase token per scheduler (stagger 2)
+  static_assert((1 + 2 * NST + 5 * NT + 1 + 4 * NT) * 8 <= 512, "barrier block");
+  float* smx = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);   // [2 parities][2 tiles][TPR][128]
+  constexpr int PW = 4 * NT * TPR, MW = PW + 1;        // producer warp / first of the NT UMMA-issuer warps
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -144,14 +158,15 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     mbar_init(q_full, 1);
-    for (int s = 0; s < NST; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 2); }
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < NST; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], NT); }
+    for (int s = 0; s < NT; ++s) {
       mbar_init(&s_full[s], 1);
       mbar_init(&p_full[s], 128 * TPR);
       mbar_init(&o_full[s], 1);
       mbar_init(&s_read[s], 128 * TPR);
+      mbar_init(&stag[s], 128 * TPR);
+      for (int q = 0; q < 4; ++q) mbar_init(&tok[s * 4 + q], TPR);
     }
-    mbar_init(stag, 128 * TPR);
     fence_barrier_init();
   }
   if (warp == MW) {
@@ -164,16 +179,16 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp >= PW) {
-  asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+  if (NT == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
   if (warp == PW) {
     // ===================== TMA producer (whole warp loops; one elected lane issues) =====================
     if (elect_one()) {
-      mbar_arrive_expect_tx(q_full, 2 * NS * QSLAB);
+      mbar_arrive_expect_tx(q_full, NT * NS * QSLAB);
 #pragma unroll
-      for (int t = 0; t < 2; ++t)
+      for (int t = 0; t < NT; ++t)
 #pragma unroll
         for (int s = 0; s < NS; ++s)
-          tma_load_3d(sQ + (t * NS + s) * QSLAB, &tmQ, q_full, hd * DP + s * 64, (2 * qt + t) * 128, n);
+          tma_load_3d(sQ + (t * NS + s) * QSLAB, &tmQ, q_full, hd * DP + s * 64, (NT * qt + t) * 128, n);
     }
     __syncwarp();
     int st = 0;
@@ -191,7 +206,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       __syncwarp();
       if (++st == NST) { st = 0; ph ^= 1; }
     }
-  } else if (warp == MW || warp == MW + 1) {
+  } else if (warp >= MW && warp < MW + NT) {
     // ===================== UMMA issuers =====================
     const uint32_t idesc_s = umma_idesc((uint32_t)BN, false, 1u);
     const uint32_t idesc_o = umma_idesc((uint32_t)DP, true, 1u);
@@ -202,7 +217,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int kk = 0; kk < p.dk16; ++kk) {
           const uint64_t adesc = umma_desc_k_sw128(sQ_a + (uint32_t)((t * NS + (kk >> 2)) * QSLAB)) + (uint64_t)(2 * (kk & 3));
           const uint64_t bdesc = umma_desc_k_sw128(sK_a + (uint32_t)((st * NS + (kk >> 2)) * KSLAB)) + (uint64_t)(2 * (kk & 3));
-          umma_f16_ss(tmem_base + (t ? S_COL1 : S_COL0), adesc, bdesc, idesc_s, kk > 0 ? 1u : 0u);
+          umma_f16_ss(tmem_base + S_COL(t), adesc, bdesc, idesc_s, kk > 0 ? 1u : 0u);
         }
         umma_commit(&s_full[t]);
       }
@@ -215,11 +230,11 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int kk = 0; kk < BN / 16; ++kk) {
           const uint64_t bdesc = umma_desc_mn_sw128(sV_a + (uint32_t)(st * NS * KSLAB + kk * 2048), (uint32_t)KSLAB);
           if (PT) {
-            umma_f16_ts(tmem_base + (t ? O_COL1 : O_COL0), tmem_base + (t ? P_COL1 : P_COL0) + (uint32_t)(kk * 8), bdesc,
+            umma_f16_ts(tmem_base + O_COL(t), tmem_base + P_COL(t) + (uint32_t)(kk * 8), bdesc,
                         idesc_o, (first && kk == 0) ? 0u : 1u);
           } else {
             const uint64_t adesc = umma_desc_k_sw128(sP_a + (uint32_t)((t * PS + (kk >> 2)) * QSLAB)) + (uint64_t)(2 * (kk & 3));
-            umma_f16_ss(tmem_base + (t ? O_COL1 : O_COL0), adesc, bdesc, idesc_o, (first && kk == 0) ? 0u : 1u);
+            umma_f16_ss(tmem_base + O_COL(t), adesc, bdesc, idesc_o, (first && kk == 0) ? 0u : 1u);
           }
         }
         umma_commit(&o_full[t]);
@@ -259,7 +274,8 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   }
   } else {
     // ===================== softmax: 4*TPR warps per query tile; TPR threads share a query row ====
-    if (TPR == 1) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    if (NT == 3) {}                              // 16 warps x 128 registers: nothing to move
+    else if (TPR == 1) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");   // 512*104 + 128*40 <= 640*96 (the CTA's own allocation)
     constexpr int HC = BN / TPR;                 // score columns per thread
     constexpr int OC = DP / TPR;                 // O columns per thread (rescale, normalisation)
@@ -269,9 +285,9 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
-    const uint32_t s_tmem = tmem_base + lane_addr + (t ? S_COL1 : S_COL0) + (uint32_t)(hf * HC);
-    const uint32_t o_tmem = tmem_base + lane_addr + (t ? O_COL1 : O_COL0);
-    const uint32_t p_tmem = tmem_base + lane_addr + (t ? P_COL1 : P_COL0) + (uint32_t)(hf * (HC / 2));
+    const uint32_t s_tmem = tmem_base + lane_addr + S_COL(t) + (uint32_t)(hf * HC);
+    const uint32_t o_tmem = tmem_base + lane_addr + O_COL(t);
+    const uint32_t p_tmem = tmem_base + lane_addr + P_COL(t) + (uint32_t)(hf * (HC / 2));
     const uint32_t p_row = smem_u32(sP + t * PS * QSLAB) + (uint32_t)(row * 128);
     const int sw = row & 7;
     const float sc = p.scale_log2;
@@ -312,7 +328,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         // the lazy rescale): exponentials against the OLD maximum, packed at once, with the row maximum computed in
         // the shadow of the MUFU pipe instead of in a phase of its own.  The scores stay in registers; a row whose
         // maximum did grow past the slack recomputes from them below -- same values as the non-speculative order.
-        if (p.stagger && j == 0 && t == 1) mbar_wait(stag, 0);
+        if (p.stagger == 1 && j == 0 && t > 0) mbar_wait(&stag[t - 1], 0);
         const float neg_old = -m_used;
         float mx8[8];
 #pragma unroll
@@ -359,7 +375,14 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       mx *= sc;
       k3 = fa_clock();
       c_max += k3 - k2;
-      if (p.stagger && j == 0 && t == 1) mbar_wait(stag, 0);      // tile B starts its exponentials after tile A's
+      if (p.stagger == 1 && j == 0 && t > 0) mbar_wait(&stag[t - 1], 0);      // tile B starts its exponentials after tile A's
+      if (p.stagger == 2) {
+        // round-robin token per scheduler: the exponent phases of the NT warps that share a MUFU pipe never overlap.
+        // Measured SLOWER (1.87 vs 1.67 ms, same box): one warp alone does not saturate the pipe (~570 cycles per 64
+        // exponentials against 448 of MUFU time), so serialising the phases costs more than the contention it removes.
+        if (t > 0) mbar_wait(&tok[(t - 1) * 4 + quarter], j & 1);
+        else if (j > 0) mbar_wait(&tok[(NT - 1) * 4 + quarter], (j - 1) & 1);
+      }
       // lazy rescale: keep the old reference maximum unless this row's maximum grew by more than 2^8
       need = mx > m_used + 8.0f;
       m_new = need ? mx : m_used;
@@ -374,10 +397,21 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int i = 0; i < HC / 2; ++i) pk[i] = pack_p<VS>(s[2 * i], s[2 * i + 1]);
       }
       }
-      if (p.stagger && j == 0 && t == 0) mbar_arrive(stag);
+      if (p.stagger == 1 && j == 0) mbar_arrive(&stag[t]);
+      if (p.stagger == 2) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tok[t * 4 + quarter]);
+      }
       const float sum = ((sum8[0] + sum8[1]) + (sum8[2] + sum8[3])) + ((sum8[4] + sum8[5]) + (sum8[6] + sum8[7]));
       const long long k4 = fa_clock();
       c_exp += k4 - k3;
+#ifdef B200AD_GEMM_PROFILE
+      // timeline of the exponent phases of key tiles 8..15 (start, end per query tile) for tools/fa_waits.py
+      if (p.dbg && j >= 8 && j < 16 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (warp & 3) == 0 && lane == 0) {
+        p.dbg[64 + t * 16 + (j - 8) * 2] = k3;
+        p.dbg[64 + t * 16 + (j - 8) * 2 + 1] = k4;
+      }
+#endif
       // PV(j-1) must be complete before P is overwritten or O rescaled
       if (j > 0) {
         mbar_wait(&o_full[t], (j - 1) & 1);
@@ -450,7 +484,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         if (i == (p.d & 31)) lv = __uint_as_float(r[i]);
       inv = 1.f / lv;
     }
-    const int qrow = (2 * qt + t) * 128 + row;
+    const int qrow = (NT * qt + t) * 128 + row;
     bf16* orow = p.out + ((long long)n * p.Lq + qrow) * p.ldo + hd * p.d;
 #pragma unroll 1
     for (int c = hf * OC; c < (hf + 1) * OC; c += 32) {
@@ -476,7 +510,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   }
 }
 
-template <int DP, int BN, bool VS, int TPR, bool PT>
+template <int DP, int BN, bool VS, int TPR, bool PT, int NT = 2>
 static int launch_attn_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                           int nbatch, int heads, int L, int d, void* out, long long ldo, cudaStream_t stream) {
   constexpr int NS = DP / 64;
@@ -508,16 +542,16 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   p.out = reinterpret_cast<bf16*>(out);
   p.ldo = ldo;
   // slabs + alignment + barriers + row-maximum exchange of the two-threads-per-row variant
-  const size_t smem = (size_t)(2 * NS * 128 * 128 + 2 * fa_nst(TPR, PT) * NS * BN * 128 + (PT ? 0 : 2 * (BN / 64) * 128 * 128)) +
-                      1024 + 256 + (TPR == 2 ? 4096 : 0);
+  const size_t smem = (size_t)(NT * NS * 128 * 128 + 2 * fa_nst(TPR, PT, NT) * NS * BN * 128 + (PT ? 0 : 2 * (BN / 64) * 128 * 128)) +
+                      1024 + 512 + (TPR == 2 ? 4096 : 0);
   B200AD_REQUIRE(smem <= 232448, "attention: %zu bytes of shared memory", smem);
   static bool attr = false;
   if (!attr) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN, VS, TPR, PT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_fa_kernel<DP, BN, VS, TPR, PT, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr = true;
   }
-  dim3 grid(L / 256, heads, nbatch);
-  attn_fa_kernel<DP, BN, VS, TPR, PT><<<grid, fa_threads(TPR), smem, stream>>>(tmQ, tmK, tmV, p);
+  dim3 grid((L + 128 * NT - 1) / (128 * NT), heads, nbatch);
+  attn_fa_kernel<DP, BN, VS, TPR, PT, NT><<<grid, fa_threads(TPR, NT), smem, stream>>>(tmQ, tmK, tmV, p);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -545,6 +579,14 @@ int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk
     return vs ? launch_attn_fa<DPV, BNV, true, 2, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)    \
               : launch_attn_fa<DPV, BNV, false, 2, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);  \
   } while (0)
+  // three query tiles per CTA (d <= 64 only: TMEM holds 3 x (S 64 + O 64 + P 32) columns)
+  // measured at L=4096 d=40 (profiles/kbench_attention_variants_r01.txt): 1.56 vs 1.62-1.70 ms with the V ones
+  // column, but 1.74-1.85 vs 1.66-1.71 ms with the explicit row sum -> three tiles only with the ones column
+  static const int nt_env = getenv("B200AD_FA_NT") ? atoi(getenv("B200AD_FA_NT")) : 0;
+  const int nt = nt_env ? nt_env : (vs ? 3 : 2);
+  if (dpad == 64 && nt == 3 && tpr == 1 && pt)
+    return vs ? launch_attn_fa<64, 64, true, 1, true, 3>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
+              : launch_attn_fa<64, 64, false, 1, true, 3>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
   if (dpad == 64) FA_LAUNCH(64, 128);
   if (dpad == 128) FA_LAUNCH(128, 64);
 #undef FA_LAUNCH
