@@ -112,6 +112,7 @@ template <int DP, int BN, bool VS, int TPR, bool PT, int NT>
 __global__ void __launch_bounds__(fa_threads(TPR, NT), 1)
 attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ FaParams p) {
+  pdl_trigger();
   constexpr int NS = DP / 64;                    // 64-column slabs per operand row
   // K/V ring depth.  Four stages (everything the 227 KB allow) when one thread owns a row: with three, a K/V tile is
   // requested only ~1.4 key tiles before its S MMA, which pulls the two query tiles back into lock-step whenever one
@@ -177,6 +178,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                            // everything above overlapped the previous kernel's tail
 
   if (warp >= PW) {
   if (NT == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
@@ -551,7 +553,7 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
     attr = true;
   }
   dim3 grid((L + 128 * NT - 1) / (128 * NT), heads, nbatch);
-  attn_fa_kernel<DP, BN, VS, TPR, PT, NT><<<grid, fa_threads(TPR, NT), smem, stream>>>(tmQ, tmK, tmV, p);
+  pdl_launch(attn_fa_kernel<DP, BN, VS, TPR, PT, NT>, dim3(grid), dim3(fa_threads(TPR, NT)), (size_t)(smem), (cudaStream_t)(stream), tmQ, tmK, tmV, p);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -36,6 +36,7 @@ template <int DP, int NST>
 __global__ void __launch_bounds__(ATT_THREADS, (DP == 64) ? 2 : 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ AttnParams p) {
+  pdl_trigger();
   constexpr int NS = DP / 64;                  // 64-column slabs per operand tile
   constexpr uint32_t TMEM_COLS = (128 + DP <= 256) ? 256u : 512u;
   constexpr uint32_t O_COL = 128;
@@ -78,6 +79,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                            // everything above overlapped the previous kernel's tail
 
   if (warp == 0) {
     if (lane == 0) {
@@ -274,7 +276,7 @@ static int launch_attn_tc(const void* q, long long ldq, const void* k, long long
     attr = true;
   }
   dim3 grid((Lq + 127) / 128, heads, nbatch);
-  attn_tc_kernel<DP, NST><<<grid, ATT_THREADS, smem, stream>>>(tmQ, tmK, tmV, p);
+  pdl_launch(attn_tc_kernel<DP, NST>, dim3(grid), dim3(ATT_THREADS), (size_t)(smem), (cudaStream_t)(stream), tmQ, tmK, tmV, p);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace b200ad {
@@ -322,6 +323,41 @@ __host__ __device__ __forceinline__ uint32_t umma_idesc(uint32_t n, bool b_mn_ma
   d |= (n >> 3) << 17;                // n_dim
   d |= (128u >> 4) << 24;             // m_dim
   return d;
+}
+
+// ----------------------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the library can be launched with cudaLaunchAttributeProgrammaticStreamSerialization (pdl_launch)
+// and starts with pdl_trigger(): the NEXT kernel of the stream may be scheduled as soon as every CTA of this one has
+// started, so its CTAs take the SMs this grid's tail leaves idle and run their prologue (barrier init, TMEM
+// allocation, tensor-map prefetch) there.  pdl_wait() then blocks until the previous grid has completed and its
+// writes are visible; it stands before the first global read or write of anything a kernel of the step produces, so
+// the data dependences are exactly those of plain stream order.  (Captured into the CUDA graph as programmatic edges.)
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() { pdl_trigger(); pdl_wait(); }
+
+// Measured inside the captured denoise step (same box, bench.py): 55.55 / 55.75 ms per step with the attribute,
+// 55.10 ms without -- kernel-to-kernel edges of a CUDA graph are already cheap and the early-resident CTAs buy
+// nothing -- so the attribute is OFF unless B200AD_PDL=1 (without it griddepcontrol.* are no-ops).
+inline bool pdl_enabled() {
+  static const bool on = getenv("B200AD_PDL") && atoi(getenv("B200AD_PDL")) != 0;
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t pdl_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 }  // namespace b200ad

@@ -23,6 +23,7 @@ __device__ __forceinline__ float2 gn_load_pair(const float* x0, int c0, const fl
 
 __global__ void gn_stats_kernel(const float* __restrict__ x0, int c0, const float* __restrict__ x1, int c1, int hw,
                                 int groups, float2* __restrict__ partial) {
+  pdl_enter();
   extern __shared__ float2 sh[];          // [npairs]
   const int C = c0 + c1;
   const int npairs = C >> 1;
@@ -60,6 +61,7 @@ __global__ void gn_stats_kernel(const float* __restrict__ x0, int c0, const floa
 // One warp per (statistic index, group): deterministic fp64 reduction of the per-block partial sums.
 __global__ void gn_finalize_kernel(const float2* __restrict__ partial, int nblk, int frames_per_stat, int groups,
                                    int hw, int cpg, float eps, float2* __restrict__ meanrstd, int nstat) {
+  pdl_enter();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= nstat * groups) return;
@@ -90,6 +92,7 @@ __global__ void gn_apply_kernel(const float* __restrict__ x0, int c0, const floa
                                 int groups, const float2* __restrict__ meanrstd, int frames_per_stat,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, int silu,
                                 T* __restrict__ out, T* __restrict__ raw) {
+  pdl_enter();
   __shared__ float s_mean[64], s_rstd[64];
   const int C = c0 + c1;
   const int npairs = C >> 1;
@@ -142,6 +145,7 @@ static constexpr int GN_SB = 1;            // 32-row sub-blocks per thread block
 
 __global__ void gn_stats_vec_kernel(const float* __restrict__ x0, int c0, const float* __restrict__ x1, int c1, int hw,
                                     int groups, int R, float2* __restrict__ partial) {
+  pdl_enter();
   extern __shared__ float2 sh[];          // [R][C]
   const int C = c0 + c1;
   const int nvec = C >> 2;
@@ -191,6 +195,7 @@ __global__ void gn_apply_vec_kernel(const float* __restrict__ x0, int c0, const 
                                     int groups, int R, const float2* __restrict__ meanrstd, int frames_per_stat,
                                     const float* __restrict__ gamma, const float* __restrict__ beta, int silu,
                                     T* __restrict__ out, T* __restrict__ raw) {
+  pdl_enter();
   const int C = c0 + c1;
   const int nvec = C >> 2;
   const int cpg = C / groups;
@@ -268,10 +273,10 @@ extern "C" int b200ad_gn_stats(const float* x0, int c0, const float* x1, int c1,
   if (gn_vec_ok(C, c0, groups)) {
     const int R = gn_vec_R(C);
     const dim3 vgrid((gn_nblk(hw) + GN_SB - 1) / GN_SB, nimg);
-    gn_stats_vec_kernel<<<vgrid, R * (C / 4), (size_t)R * C * sizeof(float2), (cudaStream_t)stream>>>(
+    pdl_launch(gn_stats_vec_kernel, dim3(vgrid), dim3(R * (C / 4)), (size_t)((size_t)R * C * sizeof(float2)), (cudaStream_t)((cudaStream_t)stream), 
         x0, c0, x1, c1, hw, groups, R, reinterpret_cast<float2*>(partial));
   } else
-    gn_stats_kernel<<<grid, gn_threads(C), (C / 2) * sizeof(float2), (cudaStream_t)stream>>>(
+    pdl_launch(gn_stats_kernel, dim3(grid), dim3(gn_threads(C)), (size_t)((C / 2) * sizeof(float2)), (cudaStream_t)((cudaStream_t)stream), 
         x0, c0, x1, c1, hw, groups, reinterpret_cast<float2*>(partial));
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
@@ -296,7 +301,7 @@ extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const floa
   {
     const int warps = nstat * groups;
     const int threads = 256;
-    gn_finalize_kernel<<<(warps * 32 + threads - 1) / threads, threads, 0, (cudaStream_t)stream>>>(
+    pdl_launch(gn_finalize_kernel, dim3((warps * 32 + threads - 1) / threads), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
         part, nblk, frames_per_stat, groups, hw, C / groups, eps, meanrstd, nstat);
     count_launch();
   }
@@ -304,16 +309,16 @@ extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const floa
     const int R = gn_vec_R(C);
     const dim3 vgrid((gn_nblk(hw) + GN_SB - 1) / GN_SB, nimg);
     if (op_dtype == 0)
-      gn_apply_vec_kernel<bf16><<<vgrid, R * (C / 4), 0, (cudaStream_t)stream>>>(
+      pdl_launch(gn_apply_vec_kernel<bf16>, dim3(vgrid), dim3(R * (C / 4)), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
           x0, c0, x1, c1, hw, groups, R, meanrstd, frames_per_stat, gamma, beta, silu, (bf16*)out_op, (bf16*)raw_op);
     else
-      gn_apply_vec_kernel<float><<<vgrid, R * (C / 4), 0, (cudaStream_t)stream>>>(
+      pdl_launch(gn_apply_vec_kernel<float>, dim3(vgrid), dim3(R * (C / 4)), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
           x0, c0, x1, c1, hw, groups, R, meanrstd, frames_per_stat, gamma, beta, silu, (float*)out_op, (float*)raw_op);
   } else if (op_dtype == 0)
-    gn_apply_kernel<bf16><<<grid, gn_threads(C), 0, (cudaStream_t)stream>>>(
+    pdl_launch(gn_apply_kernel<bf16>, dim3(grid), dim3(gn_threads(C)), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
         x0, c0, x1, c1, hw, groups, meanrstd, frames_per_stat, gamma, beta, silu, (bf16*)out_op, (bf16*)raw_op);
   else
-    gn_apply_kernel<float><<<grid, gn_threads(C), 0, (cudaStream_t)stream>>>(
+    pdl_launch(gn_apply_kernel<float>, dim3(grid), dim3(gn_threads(C)), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
         x0, c0, x1, c1, hw, groups, meanrstd, frames_per_stat, gamma, beta, silu, (float*)out_op, (float*)raw_op);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());

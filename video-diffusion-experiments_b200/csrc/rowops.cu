@@ -15,6 +15,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
                                                         const float* __restrict__ beta, float eps,
                                                         const float* __restrict__ pe, int hw, int frames,
                                                         T* __restrict__ out) {
+  pdl_enter();
   const int nwarps = (gridDim.x * blockDim.x) >> 5;
   const int lane = threadIdx.x & 31;
   const int npairs = C >> 1;
@@ -88,6 +89,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
 template <typename T>
 __global__ void cast_kernel(const float* __restrict__ x, int nimg, int h, int w, int C, int mode, T* __restrict__ out,
                             long long total4) {
+  pdl_enter();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total4) return;
   const int c4 = C >> 2;
@@ -120,6 +122,7 @@ __global__ void cast_kernel(const float* __restrict__ x, int nimg, int h, int w,
 template <typename T>
 __global__ void temporal_attn_kernel(const T* __restrict__ qkv, int F, int hw, int C, int heads, int hpb,
                                      T* __restrict__ out) {
+  pdl_enter();
   extern __shared__ float sm[];
   const int d = C / heads;
   const int W = hpb * d;                    // columns of this head group
@@ -201,7 +204,7 @@ extern "C" int b200ad_layernorm(int op_dtype, const float* x, int rows, int C, c
   const int blocks = (int)(want < (long long)sms * per_sm ? want : (long long)sms * per_sm);
   cudaStream_t st = (cudaStream_t)stream;
 #define LN_LAUNCH(TT, MP) \
-  layernorm_kernel<TT, MP><<<blocks, threads, 0, st>>>(x, rows, C, gamma, beta, eps, pe, hw, frames, (TT*)out_op)
+  pdl_launch(layernorm_kernel<TT, MP>, dim3(blocks), dim3(threads), (size_t)(0), (cudaStream_t)(st), x, rows, C, gamma, beta, eps, pe, hw, frames, (TT*)out_op)
   if (op_dtype == 0) {
     if (C <= 320) LN_LAUNCH(bf16, 5); else if (C <= 640) LN_LAUNCH(bf16, 10); else LN_LAUNCH(bf16, 20);
   } else {
@@ -224,9 +227,9 @@ extern "C" int b200ad_cast(int op_dtype, const float* x, int nimg, int h, int w,
   const int threads = 256;
   const long long blocks = (total4 + threads - 1) / threads;
   if (op_dtype == 0)
-    cast_kernel<bf16><<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(x, nimg, h, w, C, mode, (bf16*)out_op, total4);
+    pdl_launch(cast_kernel<bf16>, dim3((unsigned)blocks), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), x, nimg, h, w, C, mode, (bf16*)out_op, total4);
   else
-    cast_kernel<float><<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(x, nimg, h, w, C, mode, (float*)out_op, total4);
+    pdl_launch(cast_kernel<float>, dim3((unsigned)blocks), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), x, nimg, h, w, C, mode, (float*)out_op, total4);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -254,9 +257,9 @@ extern "C" int b200ad_temporal_attention(int op_dtype, const void* qkv, int B, i
   dim3 grid(B * hw, heads / hpb);
   cudaStream_t st = (cudaStream_t)stream;
   if (op_dtype == 0)
-    temporal_attn_kernel<bf16><<<grid, threads, smem, st>>>((const bf16*)qkv, F, hw, C, heads, hpb, (bf16*)out_op);
+    pdl_launch(temporal_attn_kernel<bf16>, dim3(grid), dim3(threads), (size_t)(smem), (cudaStream_t)(st), (const bf16*)qkv, F, hw, C, heads, hpb, (bf16*)out_op);
   else
-    temporal_attn_kernel<float><<<grid, threads, smem, st>>>((const float*)qkv, F, hw, C, heads, hpb, (float*)out_op);
+    pdl_launch(temporal_attn_kernel<float>, dim3(grid), dim3(threads), (size_t)(smem), (cudaStream_t)(st), (const float*)qkv, F, hw, C, heads, hpb, (float*)out_op);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -23,6 +23,7 @@ __device__ __forceinline__ float simt_load_a(const GemmArgs& a, int row, int k) 
 }
 
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const __grid_constant__ GemmArgs a) {
+  pdl_enter();
   __shared__ float sA[SK][SB + 1];
   __shared__ float sW[SK][SB + 1];
   const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
@@ -87,7 +88,7 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const __grid_constant__ 
 int gemm_f32_simt(const GemmArgs& a, cudaStream_t stream) {
   B200AD_REQUIRE(a.N % 4 == 0, "gemm(fp32): N=%d must be a multiple of 4", a.N);
   dim3 grid((a.N + SB - 1) / SB, (a.M + SB - 1) / SB);
-  gemm_simt_kernel<<<grid, 256, 0, stream>>>(a);
+  pdl_launch(gemm_simt_kernel, dim3(grid), dim3(256), (size_t)(0), (cudaStream_t)(stream), a);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -99,6 +100,7 @@ template <int DMAX>   // per-lane output columns = DMAX/32
 __global__ void attn_simt_kernel(const float* __restrict__ q, long long ldq, const float* __restrict__ k,
                                  long long ldk, const float* __restrict__ v, long long ldv, int heads, int Lq, int Lk,
                                  int d, int dpad, int kv_div, float* __restrict__ out, long long ldo) {
+  pdl_enter();
   extern __shared__ float sm[];
   const int KC = 32;
   float* sK = sm;                    // [KC][d+1]
@@ -168,7 +170,7 @@ int attention_f32_simt(const float* q, long long ldq, const float* k, long long 
     B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_simt_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
     attr = true;
   }
-  attn_simt_kernel<192><<<grid, nw * 32, smem, stream>>>(q, ldq, k, ldk, v, ldv, heads, Lq, Lk, d, dpad, kv_div, out, ldo);
+  pdl_launch(attn_simt_kernel<192>, dim3(grid), dim3(nw * 32), (size_t)(smem), (cudaStream_t)(stream), q, ldq, k, ldk, v, ldv, heads, Lq, Lk, d, dpad, kv_div, out, ldo);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;

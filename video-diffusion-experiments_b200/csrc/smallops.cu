@@ -8,6 +8,7 @@ namespace b200ad {
 
 // Timesteps(flip_sin_to_cos=True, freq_shift=0): out[b] = [cos(t*f_i) | sin(t*f_i)], f_i = exp(-ln(1e4)*i/half)
 __global__ void timestep_sinusoid_kernel(const float* __restrict__ t, int B, int dim, float* __restrict__ out) {
+  pdl_enter();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int half = dim >> 1;
   if (i >= B * half) return;
@@ -22,6 +23,7 @@ __global__ void timestep_sinusoid_kernel(const float* __restrict__ t, int B, int
 __global__ void small_linear_kernel(const float* __restrict__ x, int M, int K, const float* __restrict__ W,
                                     const float* __restrict__ bias, int N, int silu_in, int silu_out,
                                     float* __restrict__ y) {
+  pdl_enter();
   const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (n >= N) return;
@@ -60,6 +62,7 @@ static constexpr int CIN_MAXK = 72;     // cin*9 <= 72 (cin <= 8)
 __global__ void conv_in_kernel(const float* __restrict__ sample, int B, int cin, int F, int h, int w,
                                const float* __restrict__ W, const float* __restrict__ bias, int cout,
                                float* __restrict__ out) {
+  pdl_enter();
   __shared__ float patch[CIN_PIX][CIN_MAXK];
   const int kk = cin * 9;
   const long long pix0 = (long long)blockIdx.x * CIN_PIX;
@@ -105,6 +108,7 @@ __global__ void __launch_bounds__(320) conv_in_fast_kernel(const float* __restri
                                                            int w, const float* __restrict__ W,
                                                            const float* __restrict__ bias, int cout,
                                                            float* __restrict__ out) {
+  pdl_enter();
   constexpr int KK = CIN * 9;
   static_assert(KK % 4 == 0, "patch rows are read as float4");
   __shared__ __align__(16) float patch[PIX][KK];
@@ -155,6 +159,7 @@ template <typename T>
 __global__ void conv_out_kernel(const T* __restrict__ act, int B, int F, int h, int w, int cin,
                                 const float* __restrict__ W, const float* __restrict__ bias, int cout,
                                 float* __restrict__ out) {
+  pdl_enter();
   extern __shared__ float wsm[];          // [cout][9][cin]  (re-ordered from torch [cout][cin][3][3])
   for (int i = threadIdx.x; i < cout * 9 * cin; i += blockDim.x) {
     const int c = i % cin, t = (i / cin) % 9, co = i / (9 * cin);
@@ -214,6 +219,7 @@ __global__ void __launch_bounds__(256) conv_out_mma_kernel(const bf16* __restric
                                                            int cin, const float* __restrict__ W,
                                                            const float* __restrict__ bias, int cout,
                                                            float* __restrict__ out) {
+  pdl_enter();
   extern __shared__ __align__(16) uint8_t cosm[];
   bf16* wsm = reinterpret_cast<bf16*>(cosm);              // [9][8][wrow]
   const int wrow = conv_out_wrow(cin);
@@ -286,6 +292,7 @@ __global__ void cfg_step_kernel(const float4* __restrict__ eu, const float4* __r
                                 const float4* __restrict__ lat, float g, float cx, float ce, float in_scale,
                                 const float* __restrict__ dev_coef, long long n4, float4* __restrict__ lat_out,
                                 float4* __restrict__ model_in, int copies) {
+  pdl_enter();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n4) return;
   if (dev_coef) {
@@ -312,7 +319,7 @@ using namespace b200ad;
 extern "C" int b200ad_timestep_sinusoid(const float* t, int B, int dim, float* out, void* stream) {
   B200AD_REQUIRE(dim % 2 == 0, "timestep_sinusoid: dim=%d", dim);
   const int total = B * dim / 2;
-  timestep_sinusoid_kernel<<<(total + 127) / 128, 128, 0, (cudaStream_t)stream>>>(t, B, dim, out);
+  pdl_launch(timestep_sinusoid_kernel, dim3((total + 127) / 128), dim3(128), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), t, B, dim, out);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -324,7 +331,7 @@ extern "C" int b200ad_small_linear(const float* x, int M, int K, const float* W,
   B200AD_REQUIRE(K % 4 == 0, "small_linear: K=%d must be a multiple of 4", K);
   const int threads = 256;
   const int blocks = (int)(((long long)N * 32 + threads - 1) / threads);
-  small_linear_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(x, M, K, W, b, N, silu_in, silu_out, y);
+  pdl_launch(small_linear_kernel, dim3(blocks), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), x, M, K, W, b, N, silu_in, silu_out, y);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -337,10 +344,10 @@ extern "C" int b200ad_conv_in(const float* sample, int B, int cin, int F, int h,
   const int threads = cout >= 320 ? 320 : ((cout + 31) / 32 * 32);
   if (cin == 4) {
     constexpr int PIX = 32;
-    conv_in_fast_kernel<4, PIX><<<(unsigned)((npix + PIX - 1) / PIX), threads, 0, (cudaStream_t)stream>>>(
+    pdl_launch(conv_in_fast_kernel<4, PIX>, dim3((unsigned)((npix + PIX - 1) / PIX)), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
         sample, B, F, h, w, W, bias, cout, out_nhwc);
   } else {
-    conv_in_kernel<<<(unsigned)((npix + CIN_PIX - 1) / CIN_PIX), threads, 0, (cudaStream_t)stream>>>(
+    pdl_launch(conv_in_kernel, dim3((unsigned)((npix + CIN_PIX - 1) / CIN_PIX)), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
         sample, B, cin, F, h, w, W, bias, cout, out_nhwc);
   }
   count_launch();
@@ -375,12 +382,12 @@ extern "C" int b200ad_conv_out(int op_dtype, const void* act_nhwc, int B, int F,
     const long long ngroups = (npix + 15) / 16;
     long long nb = (ngroups + 7) / 8;
     if (nb > 2LL * sms) nb = 2LL * sms;
-    conv_out_mma_kernel<<<(unsigned)nb, 256, wbytes, (cudaStream_t)stream>>>((const bf16*)act_nhwc, B, F, h, w, cin, W,
+    pdl_launch(conv_out_mma_kernel, dim3((unsigned)nb), dim3(256), (size_t)(wbytes), (cudaStream_t)((cudaStream_t)stream), (const bf16*)act_nhwc, B, F, h, w, cin, W,
                                                                             bias, cout, out_bcfhw);
   } else if (op_dtype == 0)
-    conv_out_kernel<bf16><<<(unsigned)blocks, threads, smem, (cudaStream_t)stream>>>((const bf16*)act_nhwc, B, F, h, w, cin, W, bias, cout, out_bcfhw);
+    pdl_launch(conv_out_kernel<bf16>, dim3((unsigned)blocks), dim3(threads), (size_t)(smem), (cudaStream_t)((cudaStream_t)stream), (const bf16*)act_nhwc, B, F, h, w, cin, W, bias, cout, out_bcfhw);
   else
-    conv_out_kernel<float><<<(unsigned)blocks, threads, smem, (cudaStream_t)stream>>>((const float*)act_nhwc, B, F, h, w, cin, W, bias, cout, out_bcfhw);
+    pdl_launch(conv_out_kernel<float>, dim3((unsigned)blocks), dim3(threads), (size_t)(smem), (cudaStream_t)((cudaStream_t)stream), (const float*)act_nhwc, B, F, h, w, cin, W, bias, cout, out_bcfhw);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -392,7 +399,7 @@ extern "C" int b200ad_cfg_step(const float* eps_u, const float* eps_c, const flo
   B200AD_REQUIRE(n % 4 == 0, "cfg_step: n=%lld must be a multiple of 4", n);
   const long long n4 = n / 4;
   const int threads = 256;
-  cfg_step_kernel<<<(unsigned)((n4 + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
+  pdl_launch(cfg_step_kernel, dim3((unsigned)((n4 + threads - 1) / threads)), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
       (const float4*)eps_u, (const float4*)eps_c, (const float4*)latents, g, cx, ce, in_scale, nullptr, n4,
       (float4*)latents_out, (float4*)model_in, model_in_copies);
   count_launch();
@@ -407,7 +414,7 @@ extern "C" int b200ad_cfg_step_dev(const float* eps_u, const float* eps_c, const
   B200AD_REQUIRE(dev_coef4 && ((uintptr_t)dev_coef4 & 15) == 0, "cfg_step_dev: coefficient pointer must be 16-byte aligned");
   const long long n4 = n / 4;
   const int threads = 256;
-  cfg_step_kernel<<<(unsigned)((n4 + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
+  pdl_launch(cfg_step_kernel, dim3((unsigned)((n4 + threads - 1) / threads)), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
       (const float4*)eps_u, (const float4*)eps_c, (const float4*)latents, 0.f, 0.f, 0.f, 0.f, dev_coef4, n4,
       (float4*)latents_out, (float4*)model_in, model_in_copies);
   count_launch();

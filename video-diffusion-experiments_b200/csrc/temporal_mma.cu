@@ -40,6 +40,7 @@ template <int FT>
 __global__ void __launch_bounds__(256)
 temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int d, int hpb, int PB, int npos,
                          float scale_log2, bf16* __restrict__ out) {
+  pdl_enter();
   extern __shared__ __align__(16) uint8_t tsm[];
   constexpr int FP = 16 * FT;
   const int W = hpb * d;                 // columns of this head group, per part
@@ -240,9 +241,9 @@ int temporal_attention_bf16_mma(const bf16* qkv, int B, int F, int hw, int C, in
   dim3 grid((npos + PB - 1) / PB, heads / hpb);
   const float sl2 = 1.4426950408889634f / sqrtf((float)d);
   if (FT == 1)
-    temporal_attn_mma_kernel<1><<<grid, threads, smem, st>>>(qkv, F, hw, C, d, hpb, PB, npos, sl2, out);
+    pdl_launch(temporal_attn_mma_kernel<1>, dim3(grid), dim3(threads), (size_t)(smem), (cudaStream_t)(st), qkv, F, hw, C, d, hpb, PB, npos, sl2, out);
   else
-    temporal_attn_mma_kernel<2><<<grid, threads, smem, st>>>(qkv, F, hw, C, d, hpb, PB, npos, sl2, out);
+    pdl_launch(temporal_attn_mma_kernel<2>, dim3(grid), dim3(threads), (size_t)(smem), (cudaStream_t)(st), qkv, F, hw, C, d, hpb, PB, npos, sl2, out);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
