@@ -176,7 +176,9 @@ def _attn_ref(q, k, v):
     (2, 8, 256, 256, 40, 64, 1), (3, 2, 1024, 1024, 40, 64, 1), (2, 8, 64, 64, 160, 192, 1),
     (2, 4, 256, 256, 80, 128, 1), (4, 8, 256, 77, 40, 64, 2), (2, 8, 64, 77, 160, 192, 2),
     (1, 2, 200, 300, 8, 64, 1), (2, 8, 1024, 77, 80, 128, 1), (2, 2, 1024, 1024, 80, 128, 1),
-    (1, 2, 512, 512, 40, 64, 1), (1, 1, 2304, 2304, 80, 128, 1), (1, 2, 768, 768, 24, 64, 1)])
+    (1, 2, 512, 512, 40, 64, 1), (1, 1, 2304, 2304, 80, 128, 1), (1, 2, 768, 768, 24, 64, 1),
+    # single key tile (persistent cross-attention kernel): ragged query count, key counts 16 / 50 / 128, many tiles per CTA
+    (3, 2, 200, 50, 40, 64, 1), (2, 4, 384, 128, 80, 128, 2), (2, 2, 640, 16, 160, 192, 1), (16, 8, 4096, 77, 40, 64, 16)])
 def test_attention(mode, tol, nb, heads, Lq, Lk, d, dpad, kv_div):
     o = ops(mode)
     nkv = nb // kv_div

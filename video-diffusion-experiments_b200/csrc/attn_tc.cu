@@ -17,6 +17,9 @@ int attention_f32_simt(const float* q, long long ldq, const float* k, long long 
 int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                       int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, int v_ones, void* out,
                       long long ldo, cudaStream_t stream);   // attn_fa.cu: ping-pong kernel for the long self-attention layers
+int attention_bf16_x(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                     int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, void* out, long long ldo,
+                     cudaStream_t stream);   // attn_x.cu: persistent kernel for Lk <= 128 (text cross-attention)
 
 static constexpr int ATT_THREADS = 192;
 static constexpr int SLAB = 128 * 128;   // bytes of one [128 rows x 64 bf16] swizzled slab
@@ -311,6 +314,10 @@ extern "C" int b200ad_attention2(int op_dtype, const void* q, long long ldq, con
   {
     const int rc = attention_bf16_fa(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, flags & 1, out_op, ldo, st);
     if (rc <= 0) return rc;          // served (0) or failed (<0); 1 = not a shape of the ping-pong kernel
+  }
+  {
+    const int rc = attention_bf16_x(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out_op, ldo, st);
+    if (rc <= 0) return rc;          // single key tile: the persistent kernel of attn_x.cu
   }
   const bool one_tile = Lk <= 128;
   if (dpad == 64)
