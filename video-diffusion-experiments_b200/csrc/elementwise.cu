@@ -143,8 +143,13 @@ static constexpr int GN_SB = 1;            // 32-row sub-blocks per thread block
                                            // several load batches per thread) did not help at 64^2 (106.9 vs 106.1 us)
                                            // and starved the low-resolution levels of blocks (hw = 256: 44 -> 105 us)
 
+// FIN (one statistic per image, i.e. frames_per_stat == 1): the LAST block of an image to finish -- ticket from a
+// self-resetting per-image counter -- reduces the image's partial sums itself, in the order of gn_finalize_kernel
+// (same bits), so the separate finalize launch (82 per step, ~6.7 us each for a few KB of work) disappears.
+template <bool FIN>
 __global__ void gn_stats_vec_kernel(const float* __restrict__ x0, int c0, const float* __restrict__ x1, int c1, int hw,
-                                    int groups, int R, float2* __restrict__ partial) {
+                                    int groups, int R, float2* __restrict__ partial, unsigned int* __restrict__ counters,
+                                    float2* __restrict__ meanrstd, float eps) {
   pdl_enter();
   extern __shared__ float2 sh[];          // [R][C]
   const int C = c0 + c1;
@@ -187,6 +192,39 @@ __global__ void gn_stats_vec_kernel(const float* __restrict__ x0, int c0, const 
     partial[((long long)n * nblk + blk) * groups + g] = make_float2(ss, qq);
     for (int sb = 1; sb < GN_SB && blk + sb < nblk; ++sb)
       partial[((long long)n * nblk + blk + sb) * groups + g] = make_float2(0.f, 0.f);
+  }
+  if (FIN) {
+    __shared__ int s_last;
+    __threadfence();                       // this block's partial sums are visible device-wide before its ticket
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&counters[n], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      const int nblk = gn_nblk(hw);
+      const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+      for (int g = warp; g < groups; g += nw) {
+        const float2* base = partial + (long long)n * nblk * groups + g;
+        double sd = 0.0, qd = 0.0;
+        for (int i = lane; i < nblk; i += 32) {
+          const float2 e = __ldcg(&base[(long long)i * groups]);      // written by other SMs: bypass L1
+          sd += e.x; qd += e.y;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          sd += __shfl_xor_sync(0xffffffffu, sd, o);
+          qd += __shfl_xor_sync(0xffffffffu, qd, o);
+        }
+        if (lane == 0) {
+          const double cnt = (double)hw * cpg;
+          const double mean = sd / cnt;
+          double var = qd / cnt - mean * mean;
+          if (var < 0.0) var = 0.0;
+          meanrstd[n * groups + g] = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)eps)));
+        }
+      }
+      if (threadIdx.x == 0) counters[n] = 0;       // ready for the next call (the library runs on one stream)
+    }
   }
 }
 
@@ -262,8 +300,35 @@ using namespace b200ad;
 
 extern "C" int b200ad_gn_nblk(int hw) { return gn_nblk(hw); }
 
+static constexpr int GN_MAX_COUNTERS = 8192;
+// Per-device ticket counters of the fused finalize (zeroed once, self-resetting).  Not created while a stream capture
+// is in progress (cudaMalloc is illegal there): the caller then keeps the separate finalize kernel.
+static unsigned int* gn_counters(cudaStream_t st) {
+  static unsigned int* buf[16] = {};
+  static const bool on = !(getenv("B200AD_GN_FUSED_FIN") && atoi(getenv("B200AD_GN_FUSED_FIN")) == 0);
+  int dev = -1;
+  if (!on || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+  if (!buf[dev]) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return nullptr;
+    unsigned int* p = nullptr;
+    if (cudaMalloc(&p, GN_MAX_COUNTERS * sizeof(unsigned int)) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (cudaMemset(p, 0, GN_MAX_COUNTERS * sizeof(unsigned int)) != cudaSuccess) { cudaGetLastError(); cudaFree(p); return nullptr; }
+    buf[dev] = p;
+  }
+  return buf[dev];
+}
+
+static int gn_stats_launch(const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
+                           float* partial, void* stream, unsigned int* counters, float2* meanrstd, float eps);
+
 extern "C" int b200ad_gn_stats(const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
                                float* partial, void* stream) {
+  return gn_stats_launch(x0, c0, x1, c1, nimg, hw, groups, partial, stream, nullptr, nullptr, 0.f);
+}
+
+static int gn_stats_launch(const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
+                           float* partial, void* stream, unsigned int* counters, float2* meanrstd, float eps) {
   if (!x1) c1 = 0;
   const int C = c0 + c1;
   B200AD_REQUIRE(groups <= 64 && C % groups == 0 && (C / groups) % 2 == 0 && c0 % 2 == 0,
@@ -273,8 +338,12 @@ extern "C" int b200ad_gn_stats(const float* x0, int c0, const float* x1, int c1,
   if (gn_vec_ok(C, c0, groups)) {
     const int R = gn_vec_R(C);
     const dim3 vgrid((gn_nblk(hw) + GN_SB - 1) / GN_SB, nimg);
-    pdl_launch(gn_stats_vec_kernel, dim3(vgrid), dim3(R * (C / 4)), (size_t)((size_t)R * C * sizeof(float2)), (cudaStream_t)((cudaStream_t)stream), 
-        x0, c0, x1, c1, hw, groups, R, reinterpret_cast<float2*>(partial));
+    if (counters && GN_SB == 1)
+      pdl_launch(gn_stats_vec_kernel<true>, dim3(vgrid), dim3(R * (C / 4)), (size_t)R * C * sizeof(float2), (cudaStream_t)stream,
+                 x0, c0, x1, c1, hw, groups, R, reinterpret_cast<float2*>(partial), counters, meanrstd, eps);
+    else
+      pdl_launch(gn_stats_vec_kernel<false>, dim3(vgrid), dim3(R * (C / 4)), (size_t)R * C * sizeof(float2), (cudaStream_t)stream,
+                 x0, c0, x1, c1, hw, groups, R, reinterpret_cast<float2*>(partial), (unsigned int*)nullptr, (float2*)nullptr, 0.f);
   } else
     pdl_launch(gn_stats_kernel, dim3(grid), dim3(gn_threads(C)), (size_t)((C / 2) * sizeof(float2)), (cudaStream_t)((cudaStream_t)stream), 
         x0, c0, x1, c1, hw, groups, reinterpret_cast<float2*>(partial));
@@ -283,9 +352,20 @@ extern "C" int b200ad_gn_stats(const float* x0, int c0, const float* x1, int c1,
   return 0;
 }
 
+static int gn_apply_launch(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
+                           int groups, const float* partial, int frames_per_stat, float eps, const float* gamma,
+                           const float* beta, int silu, void* out_op, void* raw_op, void* stream, bool finalize);
+
 extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
                                int groups, const float* partial, int frames_per_stat, float eps, const float* gamma,
                                const float* beta, int silu, void* out_op, void* raw_op, void* stream) {
+  return gn_apply_launch(op_dtype, x0, c0, x1, c1, nimg, hw, groups, partial, frames_per_stat, eps, gamma, beta, silu,
+                         out_op, raw_op, stream, true);
+}
+
+static int gn_apply_launch(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
+                           int groups, const float* partial, int frames_per_stat, float eps, const float* gamma,
+                           const float* beta, int silu, void* out_op, void* raw_op, void* stream, bool finalize) {
   if (!x1) c1 = 0;
   const int C = c0 + c1;
   B200AD_REQUIRE(groups <= 64 && C % groups == 0 && (C / groups) % 2 == 0 && c0 % 2 == 0,
@@ -298,7 +378,7 @@ extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const floa
   // mean / rstd live in the tail of the caller's `partial` buffer (see b200ad.h)
   float2* part = reinterpret_cast<float2*>(const_cast<float*>(partial));
   float2* meanrstd = part + (long long)nimg * nblk * groups;
-  {
+  if (finalize) {
     const int warps = nstat * groups;
     const int threads = 256;
     pdl_launch(gn_finalize_kernel, dim3((warps * 32 + threads - 1) / threads), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
@@ -357,11 +437,16 @@ extern "C" int b200ad_group_norm(int op_dtype, const float* x0, int c0, const fl
     const long long roff = (long long)n0 * hw;
     const float* a0 = x0 + roff * c0;
     const float* a1 = x1 ? x1 + roff * c1 : nullptr;
-    if (int rc = b200ad_gn_stats(a0, c0, a1, c1, nn, hw, groups, partial, stream)) return rc;
+    // one statistic per image: the last statistics block of each image finalizes it (no finalize launch)
+    unsigned int* counters = nullptr;
+    if (frames_per_stat == 1 && nn <= GN_MAX_COUNTERS && gn_vec_ok(C, c0, groups) && groups <= 64)
+      counters = gn_counters((cudaStream_t)stream);
+    float2* meanrstd = reinterpret_cast<float2*>(partial) + (long long)nn * nblk * groups;
+    if (int rc = gn_stats_launch(a0, c0, a1, c1, nn, hw, groups, partial, stream, counters, meanrstd, eps)) return rc;
     char* o = reinterpret_cast<char*>(out_op) + (size_t)roff * C * esz;
     char* r = raw_op ? reinterpret_cast<char*>(raw_op) + (size_t)roff * C * esz : nullptr;
-    if (int rc = b200ad_gn_apply(op_dtype, a0, c0, a1, c1, nn, hw, groups, partial, frames_per_stat, eps, gamma, beta,
-                                 silu, o, r, stream))
+    if (int rc = gn_apply_launch(op_dtype, a0, c0, a1, c1, nn, hw, groups, partial, frames_per_stat, eps, gamma, beta,
+                                 silu, o, r, stream, counters == nullptr))
       return rc;
   }
   return 0;
