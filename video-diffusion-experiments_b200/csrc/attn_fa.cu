@@ -145,9 +145,8 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   uint64_t* s_read = o_full + NT;                      // [NT]  128 arrivals: the S tile is in registers
   uint64_t* stag = s_read + NT;                        // [NT] tile t's first exponent phase is over (stagger)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stag + NT);
-  uint64_t* tok = reinterpret_cast<uint64_t*>(tmem_slot + 2);   // [NT][4] exponent-phase token per scheduler (stagger 2)
   static_assert((1 + 2 * NST + 5 * NT + 1 + 4 * NT) * 8 <= 512, "barrier block");
-  float* smx = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);   // [2 parities][2 tiles][TPR][128]
+  float* smx = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);   // [2 parities][NT tiles][TPR][128]
   constexpr int PW = 4 * NT * TPR, MW = PW + 1;        // producer warp / first of the NT UMMA-issuer warps
 
   const int warp = threadIdx.x >> 5;
@@ -166,7 +165,6 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       mbar_init(&o_full[s], 1);
       mbar_init(&s_read[s], 128 * TPR);
       mbar_init(&stag[s], 128 * TPR);
-      for (int q = 0; q < 4; ++q) mbar_init(&tok[s * 4 + q], TPR);
     }
     fence_barrier_init();
   }
@@ -181,7 +179,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   pdl_wait();                            // everything above overlapped the previous kernel's tail
 
   if (warp >= PW) {
-  if (NT == 2) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+  if (NT == 2 && !(TPR == 2 && PT)) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
   if (warp == PW) {
     // ===================== TMA producer (whole warp loops; one elected lane issues) =====================
     if (elect_one()) {
@@ -276,7 +274,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
   }
   } else {
     // ===================== softmax: 4*TPR warps per query tile; TPR threads share a query row ====
-    if (NT == 3) {}                              // 16 warps x 128 registers: nothing to move
+    if (NT == 3 || (TPR == 2 && PT)) {}          // 16 warps x 128 / 20 or 28 warps x 72-96 registers: nothing to move
     else if (TPR == 1) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");   // 512*104 + 128*40 <= 640*96 (the CTA's own allocation)
     constexpr int HC = BN / TPR;                 // score columns per thread
@@ -296,6 +294,8 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     float m_used = -INFINITY;       // maximum (scaled, log2 units) the stored O / l are relative to
     float l = 0.f;
     long long c_sfull = 0, c_ld = 0, c_max = 0, c_exp = 0, c_ofull = 0, c_store = 0;
+    // anti-phase start: query tile t enters its loop when tile t-1 has finished its first exponent phase
+    if (p.stagger && t > 0) mbar_wait(&stag[t - 1], 0);
     const long long c_begin = fa_clock();
     for (int j = 0; j < p.nkv; ++j) {
       const long long k0 = fa_clock();
@@ -311,12 +311,9 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       mbar_arrive(&s_read[t]);
       const long long k2 = fa_clock();
       c_ld += k2 - k1;
-      const int kbase = j * BN + hf * HC;
-      if (kbase + HC > p.Lk) {
-#pragma unroll
-        for (int i = 0; i < HC; ++i)
-          if (kbase + i >= p.Lk) s[i] = -INFINITY;
-      }
+      // no key masking: the shapes served here have Lk % 256 == 0 (attention_bf16_fa), i.e. only whole key tiles.
+      // (Every branch inside this loop is a scheduling barrier for the compiler: two extra ones around the exponent
+      // loop cost 7 % of the kernel, profiles/kbench_attention_variants_r01.txt.)
       long long k3 = k2;
       uint32_t pk[PT ? HC / 2 : 1];                // PT: the packed bf16 probabilities of this row
       bool need;
@@ -330,7 +327,6 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         // the lazy rescale): exponentials against the OLD maximum, packed at once, with the row maximum computed in
         // the shadow of the MUFU pipe instead of in a phase of its own.  The scores stay in registers; a row whose
         // maximum did grow past the slack recomputes from them below -- same values as the non-speculative order.
-        if (p.stagger == 1 && j == 0 && t > 0) mbar_wait(&stag[t - 1], 0);
         const float neg_old = -m_used;
         float mx8[8];
 #pragma unroll
@@ -369,7 +365,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       if (TPR == 2) {
         // row maximum across the two column halves: both threads of a row end up with the same value, hence the
         // same rescale decision and the same reference maximum
-        float* slot = smx + (((j & 1) * 2 + t) * 2) * 128;
+        float* slot = smx + (((j & 1) * NT + t) * 2) * 128;
         slot[hf * 128 + row] = mx;
         named_bar_sync(1 + t, 128 * TPR);
         mx = fmaxf(mx, slot[(hf ^ 1) * 128 + row]);
@@ -377,14 +373,6 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       mx *= sc;
       k3 = fa_clock();
       c_max += k3 - k2;
-      if (p.stagger == 1 && j == 0 && t > 0) mbar_wait(&stag[t - 1], 0);      // tile B starts its exponentials after tile A's
-      if (p.stagger == 2) {
-        // round-robin token per scheduler: the exponent phases of the NT warps that share a MUFU pipe never overlap.
-        // Measured SLOWER (1.87 vs 1.67 ms, same box): one warp alone does not saturate the pipe (~570 cycles per 64
-        // exponentials against 448 of MUFU time), so serialising the phases costs more than the contention it removes.
-        if (t > 0) mbar_wait(&tok[(t - 1) * 4 + quarter], j & 1);
-        else if (j > 0) mbar_wait(&tok[(NT - 1) * 4 + quarter], (j - 1) & 1);
-      }
       // lazy rescale: keep the old reference maximum unless this row's maximum grew by more than 2^8
       need = mx > m_used + 8.0f;
       m_new = need ? mx : m_used;
@@ -399,11 +387,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int i = 0; i < HC / 2; ++i) pk[i] = pack_p<VS>(s[2 * i], s[2 * i + 1]);
       }
       }
-      if (p.stagger == 1 && j == 0) mbar_arrive(&stag[t]);
-      if (p.stagger == 2) {
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tok[t * 4 + quarter]);
-      }
+      mbar_arrive(&stag[t]);       // (every key tile, branch-free; the next query tile only waits for the first phase)
       const float sum = ((sum8[0] + sum8[1]) + (sum8[2] + sum8[3])) + ((sum8[4] + sum8[5]) + (sum8[6] + sum8[7]));
       const long long k4 = fa_clock();
       c_exp += k4 - k3;
@@ -414,11 +398,10 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         p.dbg[64 + t * 16 + (j - 8) * 2 + 1] = k4;
       }
 #endif
-      // PV(j-1) must be complete before P is overwritten or O rescaled
-      if (j > 0) {
-        mbar_wait(&o_full[t], (j - 1) & 1);
-        tc_fence_after();
-      }
+      // PV(j-1) must be complete before P is overwritten or O rescaled.  Branch-free: at j = 0 the wait is for the
+      // parity opposite to the barrier's initial phase and returns at once.
+      mbar_wait(&o_full[t], (j - 1) & 1);
+      tc_fence_after();
       const long long k5 = fa_clock();
       c_ofull += k5 - k4;
       if (__any_sync(0xffffffffu, need) && j > 0) {
@@ -470,7 +453,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     tc_fence_after();
     if (TPR == 2 && !VS) {
       // the two halves of a row each summed their own probabilities
-      float* slot = smx + ((p.nkv & 1) * 2 + t) * 2 * 128;
+      float* slot = smx + ((p.nkv & 1) * NT + t) * 2 * 128;
       slot[hf * 128 + row] = l;
       named_bar_sync(1 + t, 128 * TPR);
       l += slot[(hf ^ 1) * 128 + row];
@@ -545,7 +528,7 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   p.ldo = ldo;
   // slabs + alignment + barriers + row-maximum exchange of the two-threads-per-row variant
   const size_t smem = (size_t)(NT * NS * 128 * 128 + 2 * fa_nst(TPR, PT, NT) * NS * BN * 128 + (PT ? 0 : 2 * (BN / 64) * 128 * 128)) +
-                      1024 + 512 + (TPR == 2 ? 4096 : 0);
+                      1024 + 512 + (TPR == 2 ? 2 * NT * 2 * 128 * 4 : 0);
   B200AD_REQUIRE(smem <= 232448, "attention: %zu bytes of shared memory", smem);
   static bool attr = false;
   if (!attr) {
@@ -586,6 +569,9 @@ int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk
   // column, but 1.74-1.85 vs 1.66-1.71 ms with the explicit row sum -> three tiles only with the ones column
   static const int nt_env = getenv("B200AD_FA_NT") ? atoi(getenv("B200AD_FA_NT")) : 0;
   const int nt = nt_env ? nt_env : (vs ? 3 : 2);
+  if (dpad == 64 && nt == 2 && tpr == 2 && pt)
+    return vs ? launch_attn_fa<64, 128, true, 2, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
+              : launch_attn_fa<64, 128, false, 2, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
   if (dpad == 64 && nt == 3 && tpr == 1 && pt)
     return vs ? launch_attn_fa<64, 64, true, 1, true, 3>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
               : launch_attn_fa<64, 64, false, 1, true, 3>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
