@@ -33,20 +33,23 @@ struct AxParams {
 
 // KBT: compile-time bound of the key-tile height (80 for the 77 text tokens, 128 in general): sizes the per-thread
 // score row so that the softmax threads stay inside the 168 registers two CTAs per SM allow.
-template <int DP, int KBT>
+template <int DP, int KBT, bool LAST_ONLY>
 __global__ void __launch_bounds__(AX_THREADS, (DP <= 128) ? 2 : 1)
 attn_x_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
               const __grid_constant__ CUtensorMap tmV, const __grid_constant__ AxParams p) {
   pdl_trigger();
   constexpr int NS = DP / 64;                  // 64-column slabs per operand row
   constexpr int AX_QST = ax_qst(DP);
-  const int KB = p.KB;                         // key rows per tile (multiple of 16, <= 128)
+  // Key rows per tile = KBT, a compile-time constant (TMA zero-fills the rows beyond Lk): with a run-time height every
+  // 16-column chunk of the softmax below sat behind its own branch, and branches are scheduling barriers.
+  // LAST_ONLY: Lk > KBT - 16, i.e. only the last chunk holds keys to mask.
+  constexpr int KB = KBT;
   // TMEM columns: O [0, DP), S [DP, DP + KB), P [DP + KB, DP + 3 KB / 2) -- 184 at d=40, 248 at d=80 (KB = 80): two
   // CTAs per SM with 256 columns each; wider cases take all 512 (a second resident CTA then waits in tcgen05.alloc)
   constexpr uint32_t O_COL = 0, S_COL = DP;
-  const uint32_t P_COL = (uint32_t)(DP + KB);
-  const uint32_t TMEM_COLS = (DP + KB + KB / 2 <= 256) ? 256u : 512u;
-  const int KSLAB = KB * 128;                  // bytes of one [KB rows x 64 bf16] slab
+  constexpr uint32_t P_COL = (uint32_t)(DP + KB);
+  constexpr uint32_t TMEM_COLS = (DP + KB + KB / 2 <= 256) ? 256u : 512u;
+  constexpr int KSLAB = KB * 128;                  // bytes of one [KB rows x 64 bf16] slab
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -204,20 +207,17 @@ attn_x_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
       tc_fence_after();
       float s[KBT];
 #pragma unroll
-      for (int c = 0; c < KBT; c += 16)
-        if (c < KB) tmem_ld_32x32b_x16(s_tmem + c, reinterpret_cast<uint32_t*>(s + c));
+      for (int c = 0; c < KBT; c += 16) tmem_ld_32x32b_x16(s_tmem + c, reinterpret_cast<uint32_t*>(s + c));
       tmem_wait_ld();
       tc_fence_before();
       mbar_arrive(s_read);
       float mx = -INFINITY;
 #pragma unroll
       for (int c = 0; c < KBT; c += 16) {
-        if (c < KB) {
 #pragma unroll
-          for (int k = 0; k < 16; ++k) {
-            if (c + k >= p.Lk) s[c + k] = -INFINITY;
-            mx = fmaxf(mx, s[c + k]);
-          }
+        for (int k = 0; k < 16; ++k) {
+          if ((!LAST_ONLY || c + 16 == KBT) && c + k >= p.Lk) s[c + k] = -INFINITY;     // a select, not a branch
+          mx = fmaxf(mx, s[c + k]);
         }
       }
       const float neg_m = -mx * sc;
@@ -225,15 +225,13 @@ attn_x_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
       uint32_t pk[KBT / 2];
 #pragma unroll
       for (int c = 0; c < KBT; c += 16) {
-        if (c < KB) {
 #pragma unroll
-          for (int k = 0; k < 16; k += 2) {
-            float e0, e1;
-            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(fmaf(s[c + k], sc, neg_m)));
-            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(fmaf(s[c + k + 1], sc, neg_m)));
-            sum += e0 + e1;
-            pk[(c + k) >> 1] = pack_bf16x2(e0, e1);
-          }
+        for (int k = 0; k < 16; k += 2) {
+          float e0, e1;
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(fmaf(s[c + k], sc, neg_m)));
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(fmaf(s[c + k + 1], sc, neg_m)));
+          sum += e0 + e1;
+          pk[(c + k) >> 1] = pack_bf16x2(e0, e1);
         }
       }
       if (i > 0) {
@@ -243,8 +241,7 @@ attn_x_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
         epilogue(qt_prev, inv_prev);
       }
 #pragma unroll
-      for (int c = 0; c < KBT; c += 16)
-        if (c < KB) tmem_st_32x32b_x8(p_tmem + (c >> 1), pk + (c >> 1));
+      for (int c = 0; c < KBT; c += 16) tmem_st_32x32b_x8(p_tmem + (c >> 1), pk + (c >> 1));
       tmem_wait_st();
       tc_fence_before();       // orders the O loads above and the P stores before the arrive, i.e. before PV(i)
       mbar_arrive(p_full);
@@ -266,12 +263,12 @@ attn_x_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
   }
 }
 
-template <int DP, int KBT>
+template <int DP, int KBT, bool LAST_ONLY>
 static int launch_attn_x(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                          int nbatch, int heads, int Lq, int Lk, int d, int kv_div, void* out, long long ldo,
                          cudaStream_t stream) {
   constexpr int NS = DP / 64;
-  const int KB = (Lk + 15) / 16 * 16;
+  constexpr int KB = KBT;
   CUtensorMap tmQ, tmK, tmV;
   const int nkvb = (nbatch + kv_div - 1) / kv_div;
   {
@@ -298,7 +295,7 @@ static int launch_attn_x(const void* q, long long ldq, const void* k, long long 
   const size_t smem = (size_t)ax_qst(DP) * NS * QSLAB_X + (size_t)2 * NS * KB * 128 + 1024 + 128;
   static bool attr = false;
   if (!attr) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_x_kernel<DP, KBT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 1024));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(attn_x_kernel<DP, KBT, LAST_ONLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 1024));
     attr = true;
   }
   // one wave of CTAs: as many query-tile walkers per (n, head) as fill the SMs' CTA slots
@@ -313,7 +310,7 @@ static int launch_attn_x(const void* q, long long ldq, const void* k, long long 
   if (gx < 1) gx = 1;
   if (gx > p.ntiles) gx = p.ntiles;
   dim3 grid(gx, heads, nbatch);
-  pdl_launch(attn_x_kernel<DP, KBT>, grid, dim3(AX_THREADS), smem, stream, tmQ, tmK, tmV, p);
+  pdl_launch(attn_x_kernel<DP, KBT, LAST_ONLY>, grid, dim3(AX_THREADS), smem, stream, tmQ, tmK, tmV, p);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -326,8 +323,13 @@ int attention_bf16_x(const void* q, long long ldq, const void* k, long long ldk,
   static const int on = getenv("B200AD_ATTN_X") ? atoi(getenv("B200AD_ATTN_X")) : 1;
   if (!on || Lk > 128 || d % 8 != 0 || ldo % 8 != 0 || (reinterpret_cast<uintptr_t>(out) & 15)) return 1;
 #define AX_LAUNCH(DPV)                                                                                              \
-  return Lk <= 80 ? launch_attn_x<DPV, 80>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream) \
-                  : launch_attn_x<DPV, 128>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream)
+  do {                                                                                                              \
+    if (Lk <= 80)                                                                                                   \
+      return Lk > 64 ? launch_attn_x<DPV, 80, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream)   \
+                     : launch_attn_x<DPV, 80, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream); \
+    return Lk > 112 ? launch_attn_x<DPV, 128, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream)   \
+                    : launch_attn_x<DPV, 128, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream); \
+  } while (0)
   if (dpad == 64) AX_LAUNCH(64);
   if (dpad == 128) AX_LAUNCH(128);
   if (dpad == 192) AX_LAUNCH(192);
