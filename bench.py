@@ -292,10 +292,12 @@ def run_b200_arm(args):
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
                 tj = json.load(f)
-            g = tj.get("gemm_tc_kernel")
-            if g and g.get("dram_bytes"):
-                traffic = g["dram_bytes"] / g["launches"]
-                traffic_src = f"profiles/traffic.json ({g['launches']} launches of one step under ncu)"
+            # the kernel is a template over its epilogue mode: gemm_tc_kernel, gemm_tc_kernel<0>, ... are one family
+            gs = [v for k, v in tj.items() if k.split("<")[0] == "gemm_tc_kernel" and v.get("dram_bytes")]
+            if gs:
+                nl_t = sum(v["launches"] for v in gs)
+                traffic = sum(v["dram_bytes"] for v in gs) / nl_t
+                traffic_src = f"profiles/traffic.json ({nl_t} launches of one step under ncu)"
         except Exception:
             pass
         alg_bytes = sum(v["bytes"] for v in tens.values()) / max(nl, 1)

@@ -253,9 +253,17 @@ __device__ __forceinline__ void io_group_init(const TcParams& p, const EpiMaps& 
   }
 }
 
+// EPI: the epilogue's output combination as a compile-time constant -- 0 operand only, 1 residual + fp32, 2 residual +
+// fp32 + operand, 3 GEGLU operand, 4 anything else (run-time flags).  With run-time flags every chunk of the epilogue
+// loops went through five uniform branches, and a branch is a scheduling barrier (the same finding as in attn_fa.cu).
+template <int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ EpiMaps em, const __grid_constant__ TcParams p) {
+  const bool f_geglu = EPI == 4 ? (bool)p.geglu : EPI == 3;
+  const bool f_res = EPI == 4 ? (bool)p.has_res : (EPI == 1 || EPI == 2);
+  const bool f_o32 = EPI == 4 ? (bool)p.has_o32 : (EPI == 1 || EPI == 2);
+  const bool f_oop = EPI == 4 ? (bool)p.has_oop : (EPI == 0 || EPI == 2 || EPI == 3);
   pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -279,9 +287,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if (p.has_res) tma_prefetch_desc(&em.res);
-    if (p.has_o32) tma_prefetch_desc(&em.o32);
-    if (p.has_oop) tma_prefetch_desc(&em.oop);
+    if (f_res) tma_prefetch_desc(&em.res);
+    if (f_o32) tma_prefetch_desc(&em.o32);
+    if (f_oop) tma_prefetch_desc(&em.oop);
     for (int s = 0; s < p.num_stages; ++s) {
       mbar_init(&full_bar[s], 2);        // the leader's A producer and W producer each arrive with their tx bytes
       mbar_init(&empty_bar[s], 1);
@@ -424,7 +432,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // has drained hand that buffer to the chunk nbuf-1 ahead (fetch its residual / publish that it is free).
     // All per-group state lives in scalars (no indexed arrays, no divisions: this loop is the epilogue's pacemaker).
     const bool io_lane = elect_one();
-    const int AW = acc_width(p);
+    const int AW = (f_geglu ? 64 : 32);
     const int nbuf = p.nbuf;
     IoGroup G0, G1;
     io_group_init(p, em, G0, 0, smem, res_full, chunk_done, cluster_id, num_tiles, num_clusters, rank, io_lane);
@@ -436,7 +444,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++io_it) {
       const TileCoord t = tile_coord(p, tile, rank);
       const int nchunks = tile_chunks(p, t.n_tile);
-      const int ocol0 = (t.n_tile * p.BN) >> (p.geglu ? 1 : 0);
+      const int ocol0 = (t.n_tile * p.BN) >> (f_geglu ? 1 : 0);
       for (int c = 0; c < nchunks; ++c) {
         const int g = (c + io_it) & 1;
         IoGroup& G = g ? G1 : G0;
@@ -449,11 +457,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           uint8_t* ob = G.op + (size_t)G.buf * OP_BUF_BYTES;
           const int ocol = ocol0 + c * 32;
           if (p.conv) {
-            if (p.has_o32) tma_store_4d(&em.o32, fb, ocol, t.x0, t.y0, t.n0);
-            if (p.has_oop) tma_store_4d(&em.oop, ob, ocol, t.x0, t.y0, t.n0);
+            if (f_o32) tma_store_4d(&em.o32, fb, ocol, t.x0, t.y0, t.n0);
+            if (f_oop) tma_store_4d(&em.oop, ob, ocol, t.x0, t.y0, t.n0);
           } else {
-            if (p.has_o32) tma_store_2d(&em.o32, fb, ocol, t.m_tile * BM);
-            if (p.has_oop) tma_store_2d(&em.oop, ob, ocol, t.m_tile * BM);
+            if (f_o32) tma_store_2d(&em.o32, fb, ocol, t.m_tile * BM);
+            if (f_oop) tma_store_2d(&em.oop, ob, ocol, t.m_tile * BM);
           }
           tma_store_commit();
           const long long i2 = prof_clock();
@@ -463,12 +471,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           io_wait_read += prof_clock() - i2;
           // no residual: the hand-off is a bare arrive, no look-ahead cursor to maintain (a surplus arrive after
           // the group's last chunk completes a phase nobody waits for)
-          if (!p.has_res) mbar_arrive(&G.ready[G.prev_buf]);
+          if (!f_res) mbar_arrive(&G.ready[G.prev_buf]);
           else if (G.pre.tile < num_tiles)
             chunk_prefetch(p, em, G.f32 + (size_t)G.prev_buf * F32_BUF_BYTES, &G.ready[G.prev_buf], G.pre, rank);
         }
         __syncwarp();
-        if (p.has_res && G.pre.tile < num_tiles) {
+        if (f_res && G.pre.tile < num_tiles) {
           G.pre.c += 2;
           cursor_settle(p, G.pre, g, num_tiles, num_clusters, rank);
         }
@@ -490,7 +498,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int quarter = warp & 3;                // TMEM lane quarter this warp may access
     const int r = quarter * 32 + lane;           // row of the CTA tile owned by this thread
     const int et = threadIdx.x - 96;             // 0..255
-    const int AW = acc_width(p);
+    const int AW = (f_geglu ? 64 : 32);
     uint8_t* f32bufs = smem + p.off_f32 + (size_t)g * p.nbuf * F32_BUF_BYTES;
     uint8_t* opbufs = smem + p.off_op + (size_t)g * p.nbuf * OP_BUF_BYTES;
     uint64_t* rbar = res_full + g * MAX_NBUF;
@@ -542,7 +550,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tmem_wait_ld();
           const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
           const float4* bp = reinterpret_cast<const float4*>(bias_t + c * AW);
-          if (p.geglu) {
+          if (f_geglu) {
             uint32_t acc2[32];
             tmem_ld_32x32b_x32(taddr + (uint32_t)(c * AW + 32), acc2);
             tmem_wait_ld();
@@ -577,20 +585,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const long long q2 = prof_clock();
         mbar_wait(&rbar[buf], bphase);
         e_rbar += prof_clock() - q2;
-        if (p.has_res || p.has_o32) {
+        if (f_res || f_o32) {
           const uint32_t rowa = smem_u32(fb) + (uint32_t)(r * 128);
           const int sw = r & 7;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const uint32_t qa = rowa + (uint32_t)((j ^ sw) << 4);
-            if (p.has_res) {
+            if (f_res) {
               const float4 x = lds_f4(qa);
               v[4 * j] += x.x; v[4 * j + 1] += x.y; v[4 * j + 2] += x.z; v[4 * j + 3] += x.w;
             }
-            if (p.has_o32) sts_f4(qa, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            if (f_o32) sts_f4(qa, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
           }
         }
-        if (p.has_oop) {
+        if (f_oop) {
           const uint32_t rowa = smem_u32(ob) + (uint32_t)(r * 64);
           const int sw = (r >> 1) & 3;
 #pragma unroll
@@ -771,8 +779,18 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   p.off_bars = p.off_bias + 2 * 256 * 4;
   const size_t smem_bytes = (size_t)p.off_bars + 512 + 1024 /*align*/;
   B200AD_REQUIRE(smem_bytes <= (size_t)SMEM_LIMIT, "gemm: %zu bytes of shared memory", smem_bytes);
+  static const bool epi_generic = getenv("B200AD_GEMM_EPI_GENERIC") != nullptr;      // A/B switch: run-time flags only
+  const int epi = epi_generic ? 4 : (p.geglu && p.has_oop && !p.has_res && !p.has_o32)   ? 3
+                  : (!p.geglu && p.has_oop && !p.has_res && !p.has_o32) ? 0
+                  : (!p.geglu && p.has_res && p.has_o32 && !p.has_oop)  ? 1
+                  : (!p.geglu && p.has_res && p.has_o32 && p.has_oop)   ? 2
+                                                                        : 4;
   if (!g_attr_set) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     g_attr_set = true;
   }
   const long long tiles = (long long)p.num_m_pairs * p.num_n_tiles;
@@ -792,7 +810,13 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel, tmA, tmB, em, p));
+  switch (epi) {
+    case 0: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<0>, tmA, tmB, em, p)); break;
+    case 1: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<1>, tmA, tmB, em, p)); break;
+    case 2: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2>, tmA, tmB, em, p)); break;
+    case 3: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<3>, tmA, tmB, em, p)); break;
+    default: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<4>, tmA, tmB, em, p)); break;
+  }
   count_launch();
   return 0;
 }

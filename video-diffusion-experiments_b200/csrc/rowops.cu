@@ -9,7 +9,8 @@ namespace b200ad {
 // lane-strided => coalesced 256 B requests) and the NEXT row's loads already in flight while the current row goes
 // through its two shuffle reductions and its stores.  (One short-lived warp per row reached 3.9-4.5 TB/s: a warp's
 // 1.3 KB of loads, two serial 5-step reductions and the block turn-over left the memory pipe idle in between.)
-template <typename T, int MAXP>   // MAXP = max float2 per lane  (C <= 64*MAXP)
+template <typename T, int MAXP, bool PE>   // MAXP = max float2 per lane (C <= 64*MAXP); PE: positional embedding added
+                                           // (compile-time: a run-time `if (pe)` inside the store loop is a branch per pair)
 __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, int rows, int C,
                                                         const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, float eps,
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
         q += a0 * a0 + a1 * a1;
       }
     const float rstd = rsqrtf(warp_sum(q) * inv_c + eps);
-    const float* per = pe ? pe + (long long)((row / hw) % frames) * C : nullptr;
+    const float* per = PE ? pe + (long long)((row / hw) % frames) * C : nullptr;
     T* orow = out + (long long)row * C;
 #pragma unroll
     for (int j = 0; j < MAXP; ++j) {
@@ -75,7 +76,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
         const float2 bj = CACHE_GB ? b[CACHE_GB ? j : 0] : *reinterpret_cast<const float2*>(beta + 2 * pr);
         float a0 = (v[j].x - mean) * rstd * gj.x + bj.x;
         float a1 = (v[j].y - mean) * rstd * gj.y + bj.y;
-        if (per) {
+        if (PE) {
           const float2 p2 = *reinterpret_cast<const float2*>(per + 2 * pr);
           a0 += p2.x; a1 += p2.y;
         }
@@ -203,8 +204,15 @@ extern "C" int b200ad_layernorm(int op_dtype, const float* x, int rows, int C, c
   const int per_sm = C <= 320 ? 8 : (C <= 640 ? 3 : 2);      // resident blocks at 64 / 80 / 128 registers
   const int blocks = (int)(want < (long long)sms * per_sm ? want : (long long)sms * per_sm);
   cudaStream_t st = (cudaStream_t)stream;
-#define LN_LAUNCH(TT, MP) \
-  pdl_launch(layernorm_kernel<TT, MP>, dim3(blocks), dim3(threads), (size_t)(0), (cudaStream_t)(st), x, rows, C, gamma, beta, eps, pe, hw, frames, (TT*)out_op)
+#define LN_LAUNCH(TT, MP)                                                                                            \
+  do {                                                                                                               \
+    if (pe)                                                                                                          \
+      pdl_launch(layernorm_kernel<TT, MP, true>, dim3(blocks), dim3(threads), 0, st, x, rows, C, gamma, beta, eps, pe, hw, \
+                 frames, (TT*)out_op);                                                                               \
+    else                                                                                                             \
+      pdl_launch(layernorm_kernel<TT, MP, false>, dim3(blocks), dim3(threads), 0, st, x, rows, C, gamma, beta, eps, pe, hw, \
+                 frames, (TT*)out_op);                                                                               \
+  } while (0)
   if (op_dtype == 0) {
     if (C <= 320) LN_LAUNCH(bf16, 5); else if (C <= 640) LN_LAUNCH(bf16, 10); else LN_LAUNCH(bf16, 20);
   } else {
