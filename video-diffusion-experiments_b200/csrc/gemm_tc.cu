@@ -253,17 +253,17 @@ __device__ __forceinline__ void io_group_init(const TcParams& p, const EpiMaps& 
   }
 }
 
-// EPI: the epilogue's output combination as a compile-time constant -- 0 operand only, 1 residual + fp32, 2 residual +
-// fp32 + operand, 3 GEGLU operand, 4 anything else (run-time flags).  With run-time flags every chunk of the epilogue
-// loops went through five uniform branches, and a branch is a scheduling barrier (the same finding as in attn_fa.cu).
+// EPI: the epilogue's output combination as a compile-time constant -- a bit mask (8 GEGLU, 4 residual, 2 fp32 output,
+// 1 operand output) for the combinations the UNet uses, or -1 for run-time flags.  With run-time flags every chunk of
+// the epilogue loops went through five uniform branches, and a branch is a scheduling barrier (as in attn_fa.cu).
 template <int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ EpiMaps em, const __grid_constant__ TcParams p) {
-  const bool f_geglu = EPI == 4 ? (bool)p.geglu : EPI == 3;
-  const bool f_res = EPI == 4 ? (bool)p.has_res : (EPI == 1 || EPI == 2);
-  const bool f_o32 = EPI == 4 ? (bool)p.has_o32 : (EPI == 1 || EPI == 2);
-  const bool f_oop = EPI == 4 ? (bool)p.has_oop : (EPI == 0 || EPI == 2 || EPI == 3);
+  const bool f_geglu = EPI < 0 ? (bool)p.geglu : (EPI & 8) != 0;
+  const bool f_res = EPI < 0 ? (bool)p.has_res : (EPI & 4) != 0;
+  const bool f_o32 = EPI < 0 ? (bool)p.has_o32 : (EPI & 2) != 0;
+  const bool f_oop = EPI < 0 ? (bool)p.has_oop : (EPI & 1) != 0;
   pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -780,17 +780,18 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   const size_t smem_bytes = (size_t)p.off_bars + 512 + 1024 /*align*/;
   B200AD_REQUIRE(smem_bytes <= (size_t)SMEM_LIMIT, "gemm: %zu bytes of shared memory", smem_bytes);
   static const bool epi_generic = getenv("B200AD_GEMM_EPI_GENERIC") != nullptr;      // A/B switch: run-time flags only
-  const int epi = epi_generic ? 4 : (p.geglu && p.has_oop && !p.has_res && !p.has_o32)   ? 3
-                  : (!p.geglu && p.has_oop && !p.has_res && !p.has_o32) ? 0
-                  : (!p.geglu && p.has_res && p.has_o32 && !p.has_oop)  ? 1
-                  : (!p.geglu && p.has_res && p.has_o32 && p.has_oop)   ? 2
-                                                                        : 4;
+  const int epi_mask = (p.geglu ? 8 : 0) | (p.has_res ? 4 : 0) | (p.has_o32 ? 2 : 0) | (p.has_oop ? 1 : 0);
+  // instantiated: operand only (1), fp32 only (2), residual + operand (5), residual + fp32 (6), all three (7), GEGLU (9)
+  const bool epi_known = !epi_generic && (epi_mask == 1 || epi_mask == 2 || epi_mask == 5 || epi_mask == 6 ||
+                                          epi_mask == 7 || epi_mask == 9);
   if (!g_attr_set) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     g_attr_set = true;
   }
   const long long tiles = (long long)p.num_m_pairs * p.num_n_tiles;
@@ -810,12 +811,14 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  switch (epi) {
-    case 0: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<0>, tmA, tmB, em, p)); break;
+  switch (epi_known ? epi_mask : -1) {
     case 1: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<1>, tmA, tmB, em, p)); break;
     case 2: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2>, tmA, tmB, em, p)); break;
-    case 3: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<3>, tmA, tmB, em, p)); break;
-    default: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<4>, tmA, tmB, em, p)); break;
+    case 5: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<5>, tmA, tmB, em, p)); break;
+    case 6: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<6>, tmA, tmB, em, p)); break;
+    case 7: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<7>, tmA, tmB, em, p)); break;
+    case 9: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<9>, tmA, tmB, em, p)); break;
+    default: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<-1>, tmA, tmB, em, p)); break;
   }
   count_launch();
   return 0;
