@@ -8,8 +8,12 @@ Workload (config.workload): BASELINE.json configs[1] -- 16 frames 512x512 (laten
 (UNet batch 2), DDIM 25 steps, bf16 operands, random-init weights of the SD1.5 + motion-adapter v1.5-2
 architecture, synthetic latents / text embeddings.  One "step" = one denoise step of one video: UNet on both CFG
 halves + guidance combine + DDIM update (+ next step's model input).
-N > 1: one process per GPU (torchrun); GPUs are grouped in CFG-split pairs (rank 2p = uncond half, 2p+1 = cond
-half, one NCCL all-gather of the noise predictions per step); pairs work on independent videos.
+N > 1: one process per GPU (torchrun).  --layout pairs: GPUs are grouped in CFG-split pairs (rank 2p = uncond half,
+2p+1 = cond half, one NCCL all-gather of the noise predictions per step), pairs work on independent videos;
+--layout replicas: every GPU runs its own video with both CFG halves (no data-path collective).
+The reference arm runs the CPU restatement of the reference's loop body at the SAME shape, real steps, nothing
+extrapolated.  Our arm's line also carries `parity` (rel-L2 of the noise prediction at the benchmarked shape against
+the CPU oracle on identical weights) and, for pairs, `pair_latents_identical`.
 Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
@@ -31,7 +35,9 @@ UNIT = "steps/s"
 WORKLOAD = "AnimateDiff SD1.5 UNet + motion-adapter v1.5 (random init), 16 frames 512x512, 25 DDIM steps, CFG 7.5, bf16"
 FRAMES, LAT_H, LAT_W, NUM_STEPS, GUIDANCE = 16, 64, 64, 25, 7.5
 FLOPS_PER_STEP = 35.498e12          # SURVEY.md Appendix C, algorithmic FLOPs of one CFG step at this shape
-FLOPS_PER_STEP_C1 = 8.212e12        # the same at 16f 256^2 (BASELINE configs[0])
+# N > 1 layout when --layout auto: "pairs" = CFG-split GPU pairs (BASELINE configs[2], north star), "replicas" =
+# independent single-GPU videos.  Both are measured (profiles/); the faster one is the default.
+DEFAULT_LAYOUT = {2: "pairs", 4: "pairs", 8: "pairs"}
 
 
 def _peaks():
@@ -96,55 +102,82 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- CPU reference path (oracle)
-def cpu_reference_sample(n_samples: int, warmup: int, full_shape: bool):
-    """Times the CPU restatement of the reference's diffusers path (oracle/, kind 'port') on all host cores.
-    One sample = one fp32 UNetMotionModel forward of ONE CFG half (B=1, 16 frames) + the CFG combine and DDIM
-    update; a denoise step is two such halves.  full_shape: latents 64x64 (the 512^2 workload itself);
-    otherwise latents 32x32 (BASELINE configs[0], the reference's CPU-runnable case) with the step time
-    extrapolated to 512^2 by the algorithmic FLOP ratio.  Returns (steps_per_s, ms list per step, info)."""
+def _oracle_inputs(batch: int):
+    import torch
+    g = torch.Generator().manual_seed(42)
+    lat = torch.randn(1, 4, FRAMES, LAT_H, LAT_W, generator=g)
+    txt = torch.randn(2, 77, 768, generator=torch.Generator().manual_seed(43))
+    return lat, (txt if batch == 2 else txt[1:])
+
+
+def cpu_reference_steps(n_steps: int, warmup: int, unet=None):
+    """The reference's CPU path (its diffusers loop body, restated in oracle/, kind 'port') on all host cores, at the
+    workload's OWN shape: every step is one full CFG denoise step -- torch.cat([latents]*2) -> fp32 UNetMotionModel
+    forward at batch 2 (16 frames, latents LAT_H x LAT_W) -> CFG combine -> DDIM update.  Nothing is extrapolated:
+    `n_steps` real steps are timed after `warmup` real steps.  Returns (steps_per_s, ms list, info)."""
     import torch
     from oracle.unet_motion import make_oracle_unet
+    from oracle.schedulers import OracleDDIM, cfg_combine
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    if unet is None:
+        unet = make_oracle_unet(seed=0)
+    lat, txt = _oracle_inputs(2)
+    sch = OracleDDIM()
+    sch.set_timesteps(NUM_STEPS)
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + n_steps):
+            if i % NUM_STEPS == 0:
+                x = lat.clone()
+            t = int(sch.timesteps[i % NUM_STEPS])
+            t0 = time.perf_counter()
+            eps = unet(torch.cat([x] * 2), t, encoder_hidden_states=txt).sample
+            x = sch.step(cfg_combine(eps, GUIDANCE), t, x)
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt * 1e3)
+    ms = sum(times) / len(times)
+    info = {"cores": cores, "kind": "port",
+            "sample": (f"{n_steps} full CFG denoise steps (fp32 UNet forward at batch 2, {FRAMES}f, latents {LAT_H}x{LAT_W}, "
+                       f"+ CFG + DDIM) after {warmup} warm-up steps on {cores} threads; nothing extrapolated")}
+    return 1e3 / ms, times, info
+
+
+def cpu_half_forward_sample(unet, t: int):
+    """Bounded cpu_baseline sample for our arm's line: ONE warm-up and ONE timed fp32 forward of the cond CFG half
+    (B=1) at the workload's shape; a denoise step is two such halves (+ the negligible CFG/DDIM update, included).
+    Returns (steps_per_s, info, eps of the cond half) -- the eps doubles as the parity reference of the bench shape."""
+    import torch
     from oracle.schedulers import OracleDDIM
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    unet = make_oracle_unet(seed=0, round_to=None)
-    hw = LAT_H if full_shape else 32
-    g = torch.Generator().manual_seed(42)
-    lat = torch.randn(1, 4, FRAMES, hw, hw, generator=g)
-    txt = torch.randn(1, 77, 768, generator=torch.Generator().manual_seed(43))
+    lat, txt = _oracle_inputs(1)
     sch = OracleDDIM()
     sch.set_timesteps(NUM_STEPS)
-    scale = 1.0 if full_shape else FLOPS_PER_STEP / FLOPS_PER_STEP_C1
-    times = []
     with torch.no_grad():
-        for i in range(warmup + n_samples):
-            t = int(sch.timesteps[i % NUM_STEPS])
-            t0 = time.perf_counter()
-            eps = unet(lat, t, encoder_hidden_states=txt).sample
-            guided = eps + GUIDANCE * (eps - eps)
-            _ = sch.step(guided, t, lat)
-            dt = time.perf_counter() - t0
-            if i >= warmup:
-                times.append(dt * 2.0 * scale * 1e3)       # two CFG halves per denoise step
-    ms = sum(times) / len(times)
+        unet(lat, t, encoder_hidden_states=txt)                 # warm-up (page-in, oneDNN primitive caches)
+        t0 = time.perf_counter()
+        eps = unet(lat, t, encoder_hidden_states=txt).sample
+        _ = sch.step(eps, t, lat)
+        dt = time.perf_counter() - t0
     info = {"cores": cores, "kind": "port",
-            "sample": (f"{n_samples} x one fp32 CFG-half UNet forward (B=1, 16f, latents {hw}x{hw}) + CFG + DDIM on "
-                       f"{cores} threads; step = 2 halves" +
-                       ("" if full_shape else f"; extrapolated to 512^2 by the FLOP ratio {scale:.3f}"))}
-    return 1e3 / ms, times, info
+            "sample": (f"1 warm-up + 1 timed fp32 forward of one CFG half (B=1, {FRAMES}f, latents {LAT_H}x{LAT_W}) + DDIM "
+                       f"update on {cores} threads; a step = 2 halves (value = 1 / (2 x sample time))")}
+    return 1.0 / (2.0 * dt), info, eps
 
 
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    full = (args.steps + args.warmup) <= 4
-    v, times, info = cpu_reference_sample(args.steps, args.warmup, full_shape=full)
+    v, times, info = cpu_reference_steps(args.steps, args.warmup)
     ms = sum(times) / len(times)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "device": "host CPU", "threads": info["cores"]},
+            "config": {"workload": WORKLOAD.replace(", bf16", ", fp32 on the host CPU"), "device": "host CPU",
+                       "threads": info["cores"], "latents": [1, 4, FRAMES, LAT_H, LAT_W], "unet_batch": 2},
             "cpu_baseline": {"value": v, "unit": UNIT, **info},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -153,6 +186,40 @@ def run_reference_arm(args):
 
 
 # ----------------------------------------------------------------------------- our arm
+def _teardown_process_group(pipe, ok: bool):
+    """Multi-rank exit.  The captured CUDA graphs hold the pair communicator (the per-step all-gather is inside the
+    graph), so they are reset first; then the device is drained, the ranks meet, and the process group is destroyed
+    under a watchdog (a wedged NCCL finalizer must not keep torchrun alive).  A failing rank leaves with a non-zero
+    exit code."""
+    import gc
+    import torch
+    import torch.distributed as dist
+    for pl in list(pipe._plans.values()):
+        if pl.graph is not None:
+            pl.graph.reset()
+            pl.graph = None
+    pipe._plans.clear()
+    gc.collect()
+    torch.cuda.synchronize()
+    code = 0 if ok else 1
+
+    def _bail():
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(code)
+
+    wd = threading.Timer(60.0, _bail)
+    wd.daemon = True
+    wd.start()
+    try:
+        dist.barrier()
+        torch.cuda.synchronize()
+        dist.destroy_process_group()
+    finally:
+        wd.cancel()
+    return code
+
+
 def run_b200_arm(args):
     import torch
     import torch.distributed as dist
@@ -170,24 +237,60 @@ def run_b200_arm(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the b200ad path has no CPU fallback)")
     torch.cuda.set_device(local)
+    layout = args.layout
+    if layout == "auto":
+        layout = DEFAULT_LAYOUT.get(world, "pairs")
+    if world == 1:
+        layout = "single"
+    pairs = layout == "pairs"
     pair_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        if world % 2:
-            raise SystemExit("N > 1 runs CFG-split pairs: N must be even")
-        for p in range(world // 2):                      # every rank must create every group
-            g = dist.new_group([2 * p, 2 * p + 1])
-            if rank // 2 == p:
-                pair_group = g
-    n_videos = 1 if world == 1 else world // 2
+        if pairs:
+            if world % 2:
+                raise SystemExit("CFG-split pairs need an even N")
+            for p in range(world // 2):                      # every rank must create every group
+                g = dist.new_group([2 * p, 2 * p + 1])
+                if rank // 2 == p:
+                    pair_group = g
+    n_videos = world // 2 if pairs else world
+    ok = False
+    pipe = None
+    try:
+        pipe = AnimateDiffPipeline.from_pretrained("runwayml/stable-diffusion-v1-5", seed=0, with_vae=False)
+        rc = _bench_body(args, pipe, pair_group, pairs, n_videos, world, rank, local)
+        ok = rc == 0
+    except BaseException:
+        import traceback
+        traceback.print_exc()
+        if world == 1:
+            raise
+    if world > 1:
+        return _teardown_process_group(pipe, ok) if pipe is not None else 1
+    return 0 if ok else 1
 
-    pipe = AnimateDiffPipeline.from_pretrained("runwayml/stable-diffusion-v1-5", seed=0, with_vae=False)
+
+def _bench_body(args, pipe, pair_group, pairs, n_videos, world, rank, local):
+    import torch
+    import torch.distributed as dist
+    from b200ad import lib
+    from b200ad.ops import KernelProfiler, Ops
+    from b200ad.schedulers import DDIMScheduler
+
     pipe.cfg_group = pair_group
     pipe.scheduler = DDIMScheduler.from_config(pipe.scheduler.config, beta_schedule="linear", steps_offset=1,
                                                clip_sample=False)
     pipe.scheduler.set_timesteps(NUM_STEPS)
+    # CPU leg (rank 0, N = 1): the oracle UNet is built first and ITS (bf16-representable) random-init weights are
+    # loaded into the product, so that the bounded CPU sample below is also the parity reference of the bench shape
+    want_cpu = rank == 0 and world == 1 and not args.no_cpu_baseline
+    oracle = None
+    if want_cpu:
+        from oracle.unet_motion import make_oracle_unet
+        oracle = make_oracle_unet(seed=0)
+        pipe.unet.load_state_dict(oracle.state_dict())
     pipe.unet.prepack()
-    vid = rank // 2 if world > 1 else 0
+    vid = (rank // 2 if pairs else rank) if world > 1 else 0
     gen = torch.Generator().manual_seed(42 + vid)
     lat_host = torch.randn(1, 4, FRAMES, LAT_H, LAT_W, generator=gen).pin_memory()
     txt_host = torch.randn(2, 77, 768, generator=torch.Generator().manual_seed(43 + vid)).pin_memory()
@@ -255,11 +358,15 @@ def run_b200_arm(args):
         e2e_step(i)
     barrier()
     k_e2e = args.steps
+    clocks2 = ClockSampler(local)
+    if rank == 0:
+        clocks2.start()
     t0 = time.perf_counter()
     for j in range(k_e2e):
         e2e_step(j % NUM_STEPS)
     barrier()
     e2e_s = time.perf_counter() - t0
+    clk2 = clocks2.stop() if rank == 0 else None
     if world > 1:
         t = torch.tensor([e2e_s], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -267,6 +374,35 @@ def run_b200_arm(args):
     e2e_value = n_videos * k_e2e / e2e_s
     h2d = lat_host.numel() * 4 + txt_host.numel() * 4
     d2h = out_host.numel() * 4
+
+    # ---- CFG-split pair: are the two ranks' latents identical, and equal to the single-GPU step? --------
+    pair_check = None
+    if pairs:
+        new_video()
+        for i in range(3):
+            plan.step(i)
+        torch.cuda.synchronize()
+        both = [torch.empty_like(plan.latents) for _ in range(2)]
+        dist.all_gather(both, plan.latents, group=pair_group)
+        identical = bool(torch.equal(both[0], both[1]))
+        # the same three steps on ONE GPU with both CFG halves (eager, no collective), same inputs
+        from b200ad.pipeline import DenoisePlan
+        solo = DenoisePlan(pipe.unet, 2, FRAMES, LAT_H, LAT_W, use_graph=False, cfg_group=None)
+        solo.load(lat_host.cuda(), text_dev, pipe.scheduler, GUIDANCE)
+        for i in range(3):
+            solo.step(i)
+        torch.cuda.synchronize()
+        d = (solo.latents - plan.latents).float()
+        rel = float(d.norm() / solo.latents.float().norm())
+        worst_rel = torch.tensor([rel], device="cuda")
+        dist.all_reduce(worst_rel, op=dist.ReduceOp.MAX)
+        ident_all = torch.tensor([1.0 if identical else 0.0], device="cuda")
+        dist.all_reduce(ident_all, op=dist.ReduceOp.MIN)
+        pair_check = {"pair_latents_identical": bool(ident_all.item() == 1.0), "steps": 3,
+                      "pair_vs_single_gpu_rel_l2": float(worst_rel.item()),
+                      "how": "3 graph steps on the pair; all_gather of latents inside each pair (bitwise compare); the "
+                             "same 3 steps on one GPU with both CFG halves (eager); worst case over all ranks"}
+        del solo
 
     # ---- per-kernel-family roofline: one eager step with CUDA events around every launch (rank 0) ------
     fam, roof = None, None
@@ -309,26 +445,42 @@ def run_b200_arm(args):
                 "launches_per_step": nl, "avg_launch_ms": ms / max(nl, 1),
                 "share_of_step": ms / sum(v["ms"] for v in fam.values()),
                 "how": "CUDA events around every launch of one eager step (no graph), algorithmic FLOPs 2MNK"}
+        # tensor-pipe fraction per attention head-dim family and HBM fraction of the memory-bound families
+        for k, v in fam.items():
+            if k.startswith("attention_"):
+                v["frac_of_bf16_sustained"] = round(v["tflops"] / pk["bf16_tflops_sustained"], 4)
+            elif k in ("group_norm", "layernorm", "temporal_attention", "cast", "cfg_step"):
+                v["frac_of_hbm"] = round(v["gbs"] / pk["hbm_gbs"], 4)
         for v in fam.values():
             for k in ("ms", "tflops", "gbs"):
                 v[k] = round(v[k], 4)
 
-    # ---- CPU baseline (rank 0, N=1 only) --------------------------------------------------------------
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    # ---- CPU baseline + parity at the benchmarked shape (rank 0, N=1 only) ------------------------------
+    cpu, parity = None, None
+    if want_cpu:
         torch.cuda.synchronize()
-        v, _, info = cpu_reference_sample(1, 0, full_shape=True)
+        t_chk = int(pipe.scheduler._timesteps_host[0])
+        v, info, eps_ref = cpu_half_forward_sample(oracle, t_chk)
         cpu = {"value": v, "unit": UNIT, **info}
+        lat, txt = _oracle_inputs(1)
+        eps = pipe.unet(lat.cuda(), t_chk, encoder_hidden_states=txt.cuda()).sample
+        rel = float((eps.cpu() - eps_ref).norm() / eps_ref.norm())
+        parity = {"rel_l2": rel, "gate": 1e-2, "ok": rel < 1e-2, "t": t_chk,
+                  "what": f"noise prediction of the cond CFG half at the benchmarked shape (latents [1,4,{FRAMES},{LAT_H},"
+                          f"{LAT_W}]) vs the fp32 CPU oracle on identical bf16-representable weights / latents / text"}
+        if not parity["ok"]:
+            print(f"bench.py: PARITY FAILURE at the benchmarked shape: rel-L2 {rel:.3e} > 1e-2", file=sys.stderr)
 
     if rank == 0:
         pk = _peaks()
+        par = ("single GPU, both CFG halves" if world == 1 else
+               f"{world // 2} CFG-split pair(s): NCCL all-gather of noise predictions per step, independent videos per pair"
+               if pairs else f"{world} independent single-GPU replicas (both CFG halves per GPU), no data-path collective")
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "latents": [1, 4, FRAMES, LAT_H, LAT_W], "unet_batch": 2,
-                           "parallelism": "single GPU, both CFG halves" if world == 1 else
-                           f"{world // 2} CFG-split pair(s): NCCL all-gather of noise predictions per step, "
-                           "independent videos per pair",
+                           "parallelism": par, "layout": "single" if world == 1 else ("pairs" if pairs else "replicas"),
                            "l2": "working set per step (2.6 GB bf16 weights + activations) >> 126 MB L2; no flush",
                            "cuda_graph": plan.graph is not None, "residual_stream": "fp32"},
                 "videos_per_hour": value * 3600.0 / NUM_STEPS,
@@ -336,24 +488,19 @@ def run_b200_arm(args):
                 "frac_of_bf16_sustained": FLOPS_PER_STEP * value / 1e12 / world / pk["bf16_tflops_sustained"],
                 "clocks": clk,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "clocks": clk2,
                         "how": "per step: pinned-host latents+text -> device, text K/V, graph replay, latents -> host, sync"},
                 "gpu_launches": int(launches_per_step * args.steps),
                 "launches_per_step": int(launches_per_step),
-                "roofline": roof, "families": fam, "cpu_baseline": cpu}
+                "roofline": roof, "families": fam, "cpu_baseline": cpu, "parity": parity}
+        if pair_check is not None:
+            line["pair_latents_identical"] = pair_check["pair_latents_identical"]
+            line["pair_check"] = pair_check
         print(json.dumps(line), flush=True)
-    if world > 1:
-        # Tear-down: the captured CUDA graphs hold the pair communicator (the per-step all-gather is inside the graph);
-        # destroying the process group with them alive hung at exit (first 2-GPU run of this bench: JSON line
-        # printed, torchrun never returned).  Drop the graphs, drain the device, meet once more, then leave without
-        # NCCL's finalizers.
-        for pl in pipe._plans.values():
-            pl.graph = None
-        torch.cuda.synchronize()
-        dist.barrier()
-        torch.cuda.synchronize()
-        sys.stdout.flush()
-        sys.stderr.flush()
-        os._exit(0)
+    if parity is not None and not parity["ok"]:
+        return 3
+    if pair_check is not None and not pair_check["pair_latents_identical"]:
+        return 4
     return 0
 
 
@@ -366,6 +513,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--layout", default="auto", choices=["auto", "pairs", "replicas"],
+                    help="N > 1: CFG-split pairs (one video per 2 GPUs) or independent single-GPU replicas")
     # other BASELINE configs (not the default bench line): --frames 32 --latent 96 = configs[4] (32f 768^2);
     # --num-steps 15 --guidance 9.0 with --gpus 2 = configs[2]
     ap.add_argument("--frames", type=int, default=FRAMES)

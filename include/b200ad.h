@@ -134,6 +134,31 @@ int b200ad_cfg_step(const float* eps_u, const float* eps_c, const float* latents
 int b200ad_cfg_step_dev(const float* eps_u, const float* eps_c, const float* latents, const float* dev_coef4,
                         long long n, float* latents_out, float* model_in, int model_in_copies, void* stream);
 
+/* ---- conv_in with a folded per-pixel affine front end (VAE decoder: latents / scaling_factor -> post_quant_conv
+ * (1x1, cin -> cin, + bias) -> decoder.conv_in 3x3).  W: [cout, (cin+1)*9] fp32 in torch layout with an EXTRA input
+ * channel cin whose value is 1 inside the image and 0 in the zero padding, so that the 1x1 conv's bias is carried
+ * exactly through the padded 3x3 conv:  W[:, c, tap] = sum_j Win[:, j, tap] * Wpq[j, c] / s,  W[:, cin, tap] =
+ * sum_j Win[:, j, tap] * bpq[j]  (replaces AutoencoderKL.post_quant_conv + Decoder.conv_in of diffusers). */
+int b200ad_conv_in_affine(const float* sample, int B, int cin, int F, int h, int w, const float* W, const float* bias,
+                          int cout, float* out_nhwc, void* stream);
+
+/* ---- module-mode glue (the hook-visible eager mode: one diffusers sub-module = one call).
+ * mode 0: out[i] = silu(a[i]) (nn.SiLU);  mode 1: out[i] = a[i] + b[(i / div) % mod] (residual add: div = 1, mod = n;
+ * timestep-embedding add over NCHW: div = h*w, mod = N*C; positional-embedding add: div = 1, mod = F*C);
+ * mode 2: GEGLU gate, a = [rows, 2C] (h | g), n = rows*C, mod = C: out[rows, C] = h * gelu_erf(g). */
+int b200ad_eltwise(int mode, const float* a, const float* b, long long n, long long div, long long mod, float* out,
+                   void* stream);
+
+/* ---- row softmax of an fp32 score matrix into the operand type: out[r, :] = softmax(scale * s[r, :]), cols <= 8192,
+ * cols % 4 == 0 (VAE decoder mid-block attention, 1 head of d = 512: S = Q K^T by b200ad_gemm, this, P V by b200ad_gemm;
+ * replaces the softmax inside F.scaled_dot_product_attention / Attention.get_attention_scores of diffusers). */
+int b200ad_softmax_rows(int op_dtype, const float* s, long long rows, int cols, long long ld, float scale, void* out_op,
+                        long long ldo, void* stream);
+
+/* ---- VideoProcessor.postprocess_video: video [C, F, h, w] fp32 in [-1, 1] -> frames [F, h, w, C] uint8 =
+ * round(clamp(x/2 + 0.5, 0, 1) * 255)  (the frames consumed at 05_grid_search_ablation.py:169,178-179). */
+int b200ad_video_to_u8(const float* video_cfhw, int C, int F, int h, int w, unsigned char* out_fhwc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,17 +57,30 @@ class OracleDDIM:
 
 
 class OracleEuler:
-    """timestep_spacing='linspace', epsilon prediction, no churn (s_churn=0), interpolation 'linear'."""
+    """epsilon prediction, no churn (s_churn=0), interpolation 'linear'.  timestep_spacing='linspace' is the
+    reference's configuration (01_baseline_generation.py:76-80); 'leading' (+steps_offset) and 'trailing' are what
+    EulerDiscreteScheduler.from_config(pipe.scheduler.config) yields without the override."""
     order = 1
 
-    def __init__(self, beta_schedule: str = "linear", num_train: int = 1000):
+    def __init__(self, beta_schedule: str = "linear", num_train: int = 1000, timestep_spacing: str = "linspace",
+                 steps_offset: int = 0):
         self.num_train = num_train
+        self.timestep_spacing, self.steps_offset = timestep_spacing, steps_offset
         ac = _alphas_cumprod(num_train, schedule=beta_schedule)
         self.base_sigmas = (((1 - ac) / ac) ** 0.5).numpy().astype(np.float64)
+        self.sigmas = torch.from_numpy(np.concatenate([self.base_sigmas[::-1], [0.0]]).astype(np.float32))
         self.timesteps = None
 
     def set_timesteps(self, n: int):
-        ts = np.linspace(0, self.num_train - 1, n, dtype=np.float32)[::-1].copy()
+        if self.timestep_spacing == "linspace":
+            ts = np.linspace(0, self.num_train - 1, n, dtype=np.float32)[::-1].copy()
+        elif self.timestep_spacing == "leading":
+            ratio = self.num_train // n
+            ts = (np.arange(0, n) * ratio).round()[::-1].copy().astype(np.float32) + self.steps_offset
+        elif self.timestep_spacing == "trailing":
+            ts = (np.arange(self.num_train, 0, -self.num_train / n)).round().astype(np.float32) - 1
+        else:
+            raise ValueError(self.timestep_spacing)
         sig = np.interp(ts, np.arange(0, len(self.base_sigmas)), self.base_sigmas)
         sig = np.concatenate([sig, [0.0]]).astype(np.float32)
         self.sigmas = torch.from_numpy(sig)
@@ -76,7 +89,10 @@ class OracleEuler:
 
     @property
     def init_noise_sigma(self):
-        return float(self.sigmas.max())          # linspace / trailing spacing
+        m = float(self.sigmas.max())
+        if self.timestep_spacing in ("linspace", "trailing"):
+            return m
+        return (m ** 2 + 1) ** 0.5
 
     def scale_model_input(self, x, t):
         s = self.sigmas[self.step_index]

@@ -3,7 +3,7 @@
 # usage: gpurun --timeout 900 -- 'bash tools/gpu_quick.sh <tag> "cmd1" "cmd2" ...'
 tag=$1; shift
 out=gpurun_out; mkdir -p $out
-timeout 600 python -m pytest tests -m gpu -x -q > $out/pytest_$tag.log 2>&1; echo "pytest exit $?"; tail -3 $out/pytest_$tag.log
+timeout 1500 python -m pytest tests -m gpu -x -q --durations=15 > $out/pytest_$tag.log 2>&1; echo "pytest exit $?"; tail -25 $out/pytest_$tag.log
 i=0
 for c in "$@"; do
   i=$((i+1))

@@ -1,26 +1,31 @@
 """Attention-processor surface (diffusers: ``processor(attn, hidden_states, encoder_hidden_states=None,
 attention_mask=None, temb=None, **kw) -> Tensor``; north star: "keep the ... attention-processor ... surface").
 
-``B200AttnProcessor`` lets any module with ``to_q / to_k / to_v / to_out[0] / heads`` (our ``Attention`` or a stock
-diffusers ``Attention``) run its projections and softmax(QK^T)V on the b200ad kernels for a stand-alone
-``[Bt, L, C]`` call.  Inside ``UNetMotionModel.forward`` the fused plan bypasses processors (the same kernels are
-called with fused epilogues and without the layout round trip).
+``B200AttnProcessor`` is this repo's AttnProcessor2_0: it runs ``attn.to_q / to_k / to_v`` (called as modules, so
+forward hooks on them fire -- /root/reference/utils/forward_tracer.py:177-194), softmax(Q K^T / sqrt(d)) V on the
+b200ad attention kernels, then ``attn.to_out[0]`` / ``attn.to_out[1]``.  It serves the stand-alone ``[Bt, L, C]`` call
+of a product ``Attention`` (module mode) and, given a stock diffusers ``Attention`` whose projections are plain
+``torch.nn.Linear``, runs those projections on b200ad_gemm directly from the module's weights.  Inside the fused plan
+(``UNetMotionModel.forward`` without hooks) processors are bypassed: the same kernels run with fused epilogues.
 """
 from __future__ import annotations
 
 import torch
 
+from .leaf import Linear as _B200Linear
 from .ops import get_ops
 
 
-def _head_pad(w: torch.Tensor, heads: int, dpad: int) -> torch.Tensor:
-    n, k = w.shape
-    d = n // heads
-    if d == dpad:
-        return w
-    out = w.new_zeros(heads, dpad, k)
-    out[:, :d] = w.view(heads, d, k)
-    return out.view(heads * dpad, k)
+def _proj(o, lin, x):
+    """lin(x) for [Bt, L, K]: through the module when it is a b200ad leaf (hooks fire), else on b200ad_gemm from the
+    module's weights (a stock torch.nn.Linear would run cuBLAS)."""
+    if isinstance(lin, _B200Linear):
+        return lin(x)
+    bt, l, k = x.shape
+    w = lin.weight.detach().to("cuda", o.op_dtype).contiguous()
+    b = None if lin.bias is None else lin.bias.detach().to("cuda", torch.float32).contiguous()
+    y, _ = o.gemm(o.cast(x.reshape(bt * l, k).float().contiguous(), 1, 1, bt * l, k), w, bias=b, want_f32=True)
+    return y.view(bt, l, -1).to(x.dtype)
 
 
 class B200AttnProcessor:
@@ -36,21 +41,31 @@ class B200AttnProcessor:
         o = get_ops(getattr(attn, "_b200_mode", self.mode))
         x = hidden_states
         ctx = x if encoder_hidden_states is None else encoder_hidden_states
-        bt, lq, c = x.shape
+        bt, lq, _ = x.shape
         lk = ctx.shape[1]
         heads = attn.heads
-        d = attn.to_q.weight.shape[0] // heads
-        dpad = d if o.mode == "fp32" else next(p for p in (64, 128, 192) if d <= p)
-        dev = lambda w: w.detach().to("cuda", o.op_dtype).contiguous()
-        xr = o.cast(x.reshape(bt * lq, c).float().contiguous(), 1, 1, bt * lq, c)
-        cr = xr if encoder_hidden_states is None else o.cast(
-            ctx.reshape(-1, ctx.shape[-1]).float().contiguous(), 1, 1, ctx.shape[0] * lk, ctx.shape[-1])
-        _, q = o.gemm(xr, dev(_head_pad(attn.to_q.weight.detach(), heads, dpad)), want_op=True)
-        _, k = o.gemm(cr, dev(_head_pad(attn.to_k.weight.detach(), heads, dpad)), want_op=True)
-        _, v = o.gemm(cr, dev(_head_pad(attn.to_v.weight.detach(), heads, dpad)), want_op=True)
-        kv_div = bt // ctx.shape[0]
-        att = o.attention(q, k, v, bt, heads, lq, lk, d, dpad, kv_div)
-        lin = attn.to_out[0]
-        bias = None if lin.bias is None else lin.bias.detach().to("cuda", torch.float32).contiguous()
-        out, _ = o.gemm(att, dev(lin.weight), bias=bias, want_f32=True)
-        return out.view(bt, lq, -1).to(hidden_states.dtype)
+        q, k, v = _proj(o, attn.to_q, x), _proj(o, attn.to_k, ctx), _proj(o, attn.to_v, ctx)
+        c = q.shape[-1]
+        d = c // heads
+        if encoder_hidden_states is None and lq <= 32 and d % 8 == 0:
+            # short sequences, many of them (the motion module's [B*h*w, F, C]): the frame-axis kernel, one warp per
+            # (sequence, head); rows are (sequence, position)-ordered, i.e. its (b, f, hw) layout with hw = 1
+            qkv = torch.cat([q, k, v], -1).reshape(bt * lq, 3 * c).float().contiguous()
+            att = o.temporal_attention(o.cast(qkv, 1, 1, bt * lq, 3 * c), bt, lq, 1, c, heads)
+        else:
+            dpad = d if o.mode == "fp32" else next(p for p in (64, 128, 192) if d <= p)
+
+            def heads_padded(t, rows):
+                buf = torch.zeros(rows, heads, dpad, device=t.device, dtype=torch.float32)
+                buf[..., :d] = t.reshape(rows, heads, d).float()
+                return o.cast(buf.view(rows, heads * dpad), 1, 1, rows, heads * dpad)
+
+            kv_div = bt // ctx.shape[0]
+            att = o.attention(heads_padded(q, bt * lq), heads_padded(k, ctx.shape[0] * lk),
+                              heads_padded(v, ctx.shape[0] * lk), bt, heads, lq, lk, d, dpad, kv_div)
+        out = att.view(bt, lq, c).to(x.dtype)
+        out = _proj(o, attn.to_out[0], out)
+        return attn.to_out[1](out) if len(attn.to_out) > 1 else out
+
+
+AttnProcessor2_0 = B200AttnProcessor

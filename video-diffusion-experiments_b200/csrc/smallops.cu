@@ -59,12 +59,13 @@ __global__ void small_linear_kernel(const float* __restrict__ x, int M, int K, c
 // (thread = cout, weights for that cout in registers, input patch shared through smem).
 static constexpr int CIN_PIX = 16;
 static constexpr int CIN_MAXK = 72;     // cin*9 <= 72 (cin <= 8)
+// ones_ch = 1: one extra input channel (index cin) that is 1 inside the image and 0 in the padding (b200ad_conv_in_affine)
 __global__ void conv_in_kernel(const float* __restrict__ sample, int B, int cin, int F, int h, int w,
                                const float* __restrict__ W, const float* __restrict__ bias, int cout,
-                               float* __restrict__ out) {
+                               float* __restrict__ out, int ones_ch) {
   pdl_enter();
   __shared__ float patch[CIN_PIX][CIN_MAXK];
-  const int kk = cin * 9;
+  const int kk = (cin + ones_ch) * 9;
   const long long pix0 = (long long)blockIdx.x * CIN_PIX;
   const long long npix = (long long)B * F * h * w;
   for (int i = threadIdx.x; i < CIN_PIX * kk; i += blockDim.x) {
@@ -78,7 +79,7 @@ __global__ void conv_in_kernel(const float* __restrict__ sample, int B, int cin,
       const int c = k / 9, ky = (k % 9) / 3, kx = k % 3;
       const int yy = y + ky - 1, xx = x + kx - 1;
       if (yy >= 0 && yy < h && xx >= 0 && xx < w)
-        v = sample[((((long long)b * cin + c) * F + f) * h + yy) * w + xx];
+        v = c < cin ? sample[((((long long)b * cin + c) * F + f) * h + yy) * w + xx] : 1.0f;
     }
     patch[p][k] = v;
   }
@@ -348,8 +349,20 @@ extern "C" int b200ad_conv_in(const float* sample, int B, int cin, int F, int h,
         sample, B, F, h, w, W, bias, cout, out_nhwc);
   } else {
     pdl_launch(conv_in_kernel, dim3((unsigned)((npix + CIN_PIX - 1) / CIN_PIX)), dim3(threads), (size_t)(0), (cudaStream_t)((cudaStream_t)stream), 
-        sample, B, cin, F, h, w, W, bias, cout, out_nhwc);
+        sample, B, cin, F, h, w, W, bias, cout, out_nhwc, 0);
   }
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200ad_conv_in_affine(const float* sample, int B, int cin, int F, int h, int w, const float* W,
+                                     const float* bias, int cout, float* out_nhwc, void* stream) {
+  B200AD_REQUIRE((cin + 1) * 9 <= CIN_MAXK, "conv_in_affine: cin=%d too large for the direct kernel", cin);
+  const long long npix = (long long)B * F * h * w;
+  const int threads = cout >= 256 ? 256 : ((cout + 31) / 32 * 32);
+  pdl_launch(conv_in_kernel, dim3((unsigned)((npix + CIN_PIX - 1) / CIN_PIX)), dim3(threads), (size_t)(0), (cudaStream_t)stream,
+             sample, B, cin, F, h, w, W, bias, cout, out_nhwc, 1);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;

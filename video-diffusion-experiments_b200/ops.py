@@ -245,6 +245,73 @@ class Ops:
                                               out.data_ptr(), _stream()), "b200ad_conv_out")
         return out
 
+    # ---------------------------------------------------------------- module-mode glue / VAE pieces
+    def _eltwise(self, mode, a, b, n, div, mod, out):
+        _lib.check(self.L.b200ad_eltwise(mode, a.data_ptr(), _ptr(b), n, div, mod, out.data_ptr(), _stream()),
+                   "b200ad_eltwise")
+        return out
+
+    def silu(self, x):
+        _need_cuda(x)
+        assert x.dtype == torch.float32 and x.is_contiguous()
+        with self._rec("eltwise", 0.0, 2 * _nb(x)):
+            return self._eltwise(0, x, None, x.numel(), 1, 1, torch.empty_like(x))
+
+    def add(self, a, b, div: int = 1, mod=None):
+        """a + b.flat[(i // div) % mod] (mod defaults to b.numel(): plain add when b has a's size)."""
+        _need_cuda(a, b)
+        assert a.dtype == torch.float32 and b.dtype == torch.float32 and a.is_contiguous() and b.is_contiguous()
+        mod = b.numel() if mod is None else mod
+        assert mod <= b.numel() and (div != 1 or mod != b.numel() or b.numel() <= a.numel())
+        with self._rec("eltwise", 0.0, 2 * _nb(a) + _nb(b)):
+            return self._eltwise(1, a, b, a.numel(), div, mod, torch.empty_like(a))
+
+    def geglu_gate(self, hg):
+        """[rows, 2C] = (h | g) -> [rows, C] = h * gelu_erf(g)."""
+        _need_cuda(hg)
+        assert hg.dtype == torch.float32 and hg.is_contiguous() and hg.dim() == 2 and hg.shape[1] % 2 == 0
+        rows, c2 = hg.shape
+        out = torch.empty((rows, c2 // 2), device=hg.device, dtype=torch.float32)
+        with self._rec("eltwise", 0.0, _nb(hg, out)):
+            return self._eltwise(2, hg, None, out.numel(), 1, c2 // 2, out)
+
+    def softmax_rows(self, s, scale: float, out=None):
+        """softmax(scale * s) along the last axis of fp32 [rows, cols] (row stride = s.stride(0)) -> operand type."""
+        _need_cuda(s)
+        assert s.dtype == torch.float32 and s.dim() == 2 and s.stride(1) == 1
+        rows, cols = s.shape
+        if out is None:
+            out = torch.empty((rows, cols), device=s.device, dtype=self.op_dtype)
+        with self._rec("softmax_rows", 0.0, rows * cols * (4.0 + out.element_size())):
+            _lib.check(self.L.b200ad_softmax_rows(self.op, s.data_ptr(), rows, cols, s.stride(0), float(scale),
+                                                  out.data_ptr(), out.stride(0), _stream()), "b200ad_softmax_rows")
+        return out
+
+    def video_to_u8(self, video):
+        """[C, F, h, w] fp32 in [-1, 1] -> [F, h, w, C] uint8 (diffusers postprocess_video)."""
+        _need_cuda(video)
+        assert video.dtype == torch.float32 and video.is_contiguous() and video.dim() == 4
+        C, F, h, w = video.shape
+        out = torch.empty((F, h, w, C), device=video.device, dtype=torch.uint8)
+        with self._rec("video_to_u8", 0.0, _nb(video, out)):
+            _lib.check(self.L.b200ad_video_to_u8(video.data_ptr(), C, F, h, w, out.data_ptr(), _stream()),
+                       "b200ad_video_to_u8")
+        return out
+
+    def conv_in_affine(self, sample, w_aug, b):
+        """conv_in over [sample | ones] (b200ad_conv_in_affine): sample [B, cin, F, h, w], w_aug [cout, cin+1, 3, 3]."""
+        _need_cuda(sample, w_aug)
+        assert sample.dtype == torch.float32 and sample.is_contiguous() and sample.dim() == 5
+        assert w_aug.dtype == torch.float32 and w_aug.is_contiguous()
+        B, cin, F, h, wd = sample.shape
+        cout = w_aug.shape[0]
+        assert w_aug.shape[1] == cin + 1
+        out = torch.empty((B * F * h * wd, cout), device=sample.device, dtype=torch.float32)
+        with self._rec("conv_in", 2.0 * B * F * h * wd * cout * (cin + 1) * 9, _nb(sample, out)):
+            _lib.check(self.L.b200ad_conv_in_affine(sample.data_ptr(), B, cin, F, h, wd, w_aug.data_ptr(), _ptr(b), cout,
+                                                    out.data_ptr(), _stream()), "b200ad_conv_in_affine")
+        return out
+
     def cfg_step(self, eps_u, eps_c, latents, g, cx, ce, in_scale=1.0, latents_out=None, model_in=None):
         """latents' = cx*latents + ce*(eps_u + g*(eps_c-eps_u)); model_in[k] = latents'*in_scale."""
         _need_cuda(eps_u, eps_c, latents)

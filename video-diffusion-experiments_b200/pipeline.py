@@ -56,13 +56,85 @@ class MotionAdapter:
         return self
 
 
+_CKPT_NAMES = ("diffusion_pytorch_model.safetensors", "diffusion_pytorch_model.fp16.safetensors",
+               "diffusion_pytorch_model.bin", "diffusion_pytorch_model.fp16.bin")
+
+
 def _load_local_state_dict(path: str, sub: str):
+    """State dict of a local diffusers-layout directory (``<path>/<sub>/diffusion_pytorch_model[.fp16].safetensors``
+    or ``.bin``); None when the directory holds no checkpoint (this box: no network, no weights)."""
     d = os.path.join(path, sub) if sub else path
-    f = os.path.join(d, "diffusion_pytorch_model.safetensors")
-    if not os.path.isfile(f):
+    for name in _CKPT_NAMES:
+        f = os.path.join(d, name)
+        if os.path.isfile(f):
+            if name.endswith(".safetensors"):
+                from safetensors.torch import load_file
+                return load_file(f)
+            return torch.load(f, map_location="cpu", weights_only=True)
+    return None
+
+
+_LEGACY_VAE_ATTN = {"query": "to_q", "key": "to_k", "value": "to_v", "proj_attn": "to_out.0"}
+
+
+def _rename_legacy_vae_keys(sd: dict) -> dict:
+    """SD1.5's vae checkpoint stores the mid-block attention under the deprecated AttentionBlock names
+    (query/key/value/proj_attn); diffusers renames them on load, and so must we."""
+    out = {}
+    for k, v in sd.items():
+        parts = k.split(".")
+        if "attentions" in parts and len(parts) >= 2 and parts[-2] in _LEGACY_VAE_ATTN:
+            parts[-2:-1] = _LEGACY_VAE_ATTN[parts[-2]].split(".")
+            k = ".".join(parts)
+            if v.dim() == 4:                        # very old checkpoints: 1x1 conv weights
+                v = v[:, :, 0, 0]
+        out[k] = v
+    return out
+
+
+def _load_checked(module, sd: dict, what: str, allow_missing=lambda k: False, allow_unexpected=lambda k: False):
+    """load_state_dict(strict=False) that REFUSES silent partial loads: any parameter of `module` the checkpoint does
+    not provide (other than the ones `allow_missing` names) or any checkpoint key the module does not know raises."""
+    res = module.load_state_dict(sd, strict=False)
+    missing = [k for k in res.missing_keys if not allow_missing(k)]
+    unexpected = [k for k in res.unexpected_keys if not allow_unexpected(k)]
+    if missing or unexpected:
+        raise RuntimeError(
+            f"{what}: checkpoint does not match the module tree -- {len(missing)} missing "
+            f"(e.g. {missing[:3]}), {len(unexpected)} unexpected (e.g. {unexpected[:3]}); refusing to run with "
+            "partially random weights")
+    _log(f"{what}: loaded {len(sd) - len(res.unexpected_keys)} tensors"
+         + (f" ({len(res.missing_keys)} left at their init by design)" if res.missing_keys else ""))
+
+
+class _LocalClip:
+    """CLIP ViT-L/14 text encoder + tokenizer from a LOCAL diffusers-layout directory (``text_encoder/``,
+    ``tokenizer/``), as AnimateDiffPipeline loads them at /root/reference/experiments/05_grid_search_ablation.py:130-134.
+    Off the denoise path: runs once per prompt through transformers' CLIPTextModel."""
+
+    def __init__(self, tokenizer, model):
+        self.tokenizer, self.model = tokenizer, model
+
+    @torch.no_grad()
+    def __call__(self, prompt: str) -> torch.Tensor:
+        ids = self.tokenizer(prompt, padding="max_length", max_length=self.tokenizer.model_max_length,
+                             truncation=True, return_tensors="pt").input_ids
+        return self.model(ids.to(self.model.device))[0].float()          # [1, 77, 768]
+
+
+def _load_text_encoder(path: str):
+    te, tk = os.path.join(path, "text_encoder"), os.path.join(path, "tokenizer")
+    if not (os.path.isdir(te) and os.path.isdir(tk)):
+        _log(f"'{path}': no local text_encoder/ + tokenizer/ -> prompts map to synthetic text embeddings "
+             "(seeded by the prompt string)")
         return None
-    from safetensors.torch import load_file
-    return load_file(f)
+    from transformers import CLIPTextModel, CLIPTokenizer
+    tok = CLIPTokenizer.from_pretrained(tk, local_files_only=True)
+    model = CLIPTextModel.from_pretrained(te, local_files_only=True).eval()
+    if torch.cuda.is_available():
+        model = model.cuda()
+    _log(f"'{path}': CLIP text encoder loaded from the local directory")
+    return _LocalClip(tok, model)
 
 
 def synthetic_text_embeds(prompt: str, length: int = 77, dim: int = 768) -> torch.Tensor:
@@ -107,7 +179,8 @@ class DenoisePlan:
     def load(self, latents, text, scheduler, guidance_scale: float):
         """Start a video: initial latents [1,4,F,h,w] (already * init_noise_sigma), text rows, schedule table."""
         n = scheduler.num_inference_steps
-        key = (id(scheduler), type(scheduler).__name__, n, float(guidance_scale), id(scheduler._timesteps_host))
+        key = (type(scheduler).__name__, tuple(sorted((k, repr(v)) for k, v in dict(scheduler.config).items())), n,
+               float(guidance_scale), self.B)
         if key != self._table_key:
             tab = torch.zeros(n, 8)
             ts = scheduler._timesteps_host
@@ -121,6 +194,13 @@ class DenoisePlan:
         self.kv = self.unet.text_kv(self.text, out=self.kv)        # in place: the captured graph reads these
         # first model input = latents * first_in_scale, through the same kernel (eps unused: cx=1, ce=0)
         self.o32.cfg_step(self.latents, self.latents, self.latents, 0.0, 1.0, 0.0, scheduler.first_in_scale(),
+                          latents_out=self.latents, model_in=self.model_in)
+
+    def set_latents(self, latents, scheduler, i: int):
+        """Replace the latents after step i (callback_on_step_end returned new ones): also refresh the next model input."""
+        self.latents.copy_(latents.reshape(self.latents.shape).float())
+        nxt = scheduler.step_coefficients(i)[2]
+        self.o32.cfg_step(self.latents, self.latents, self.latents, 0.0, 1.0, 0.0, nxt,
                           latents_out=self.latents, model_in=self.model_in)
 
     def capture(self):
@@ -165,6 +245,7 @@ class AnimateDiffPipeline:
         self.device = torch.device("cuda") if torch.cuda.is_available() else torch.device("cpu")
         self.cfg_group = cfg_group              # 2-rank process group: CFG halves split across a GPU pair
         self.use_graph = os.environ.get("B200AD_GRAPH", "1") != "0"
+        self.text_encoder = None                # _LocalClip when a local checkpoint directory provides one
         self._plans = {}
         self.last_latents = None
 
@@ -185,20 +266,27 @@ class AnimateDiffPipeline:
             vae = AutoencoderKLDecoder() if with_vae else None
         torch.random.set_rng_state(rng)
         torch.cuda.set_rng_state(crng)
+        is_motion = lambda k: "motion_modules" in k
         sd = _load_local_state_dict(name_or_path, "unet")
         if sd is not None:
-            unet.load_state_dict(sd, strict=False)
+            # the SD1.5 UNet2DConditionModel checkpoint holds every non-motion parameter
+            _load_checked(unet, sd, f"unet of '{name_or_path}'", allow_missing=is_motion)
         else:
             _log(f"'{name_or_path}': no local checkpoint -> SD1.5 UNet + motion modules use seeded random init "
-                 f"(seed {seed}); prompts map to synthetic text embeddings")
+                 f"(seed {seed})")
         if motion_adapter is not None and motion_adapter.state_dict_ is not None:
-            unet.load_state_dict(motion_adapter.state_dict_, strict=False)
+            # a MotionAdapter checkpoint holds exactly the motion-module subset
+            _load_checked(unet, motion_adapter.state_dict_, f"motion adapter '{motion_adapter.source}'",
+                          allow_missing=lambda k: not is_motion(k))
         if vae is not None:
             vsd = _load_local_state_dict(name_or_path, "vae")
             if vsd is not None:
-                vae.load_state_dict(vsd, strict=False)
+                _load_checked(vae, _rename_legacy_vae_keys(vsd), f"vae of '{name_or_path}'",
+                              allow_unexpected=lambda k: k.startswith(("encoder.", "quant_conv.")))
         sched = _sched.PNDMPlaceholder(_sched.SD15_SCHEDULER_CONFIG)
-        return cls(unet, sched, vae, torch_dtype=torch_dtype)
+        pipe = cls(unet, sched, vae, torch_dtype=torch_dtype)
+        pipe.text_encoder = _load_text_encoder(name_or_path)
+        return pipe
 
     def to(self, *a, **kw):
         return self
@@ -222,8 +310,11 @@ class AnimateDiffPipeline:
 
     # ---- pieces of __call__ -------------------------------------------------------------------
     def encode_prompt(self, prompt, negative_prompt, do_cfg: bool):
-        pe = synthetic_text_embeds(prompt)[None]
-        ne = synthetic_text_embeds(negative_prompt or "")[None] if do_cfg else None
+        """[1,77,768] embeddings of the prompt (and of the negative prompt under CFG): the local CLIP text encoder
+        when the checkpoint directory has one, else deterministic synthetic embeddings seeded by the string."""
+        enc = self.text_encoder if self.text_encoder is not None else (lambda p: synthetic_text_embeds(p)[None])
+        pe = enc(prompt)
+        ne = enc(negative_prompt or "") if do_cfg else None
         return pe, ne
 
     def prepare_latents(self, num_frames, height, width, generator, latents=None):
@@ -247,7 +338,8 @@ class AnimateDiffPipeline:
         """The loop body of AnimateDiffPipeline.__call__ for our schedulers: latents
         [1,4,F,h,w] (already scaled by init_noise_sigma), text [B,77,768] with the uncond row first."""
         sch = self.scheduler
-        sch.set_timesteps(num_inference_steps, device=None)
+        if sch.num_inference_steps != num_inference_steps:
+            sch.set_timesteps(num_inference_steps, device=None)
         B = text.shape[0]
         _, _, F, h, w = latents.shape
         plan = self._plan(B, F, h, w)
@@ -258,16 +350,19 @@ class AnimateDiffPipeline:
         for i in range(num_inference_steps):
             plan.step(i)
             if callback is not None:
-                callback(i, sch._timesteps_host[i], plan.latents)
-        return plan.latents
+                # diffusers: callback_on_step_end(pipe, step_index, timestep, callback_kwargs) -> dict; a returned
+                # "latents" replaces the loop's latents
+                ret = callback(self, i, sch.timesteps[i], {"latents": plan.latents})
+                if isinstance(ret, dict) and ret.get("latents") is not None and ret["latents"] is not plan.latents:
+                    plan.set_latents(ret["latents"], sch, i)
+        return plan.latents.clone()              # the plan's buffer is reused by the next call
 
     @torch.no_grad()
-    def _denoise_generic(self, latents, text, guidance_scale, num_inference_steps):
+    def _denoise_generic(self, latents, text, guidance_scale, num_inference_steps, callback=None):
         """Duck-typed loop for a foreign scheduler object (set_timesteps / scale_model_input / step)."""
         sch = self.scheduler
-        sch.set_timesteps(num_inference_steps, device="cuda")
         do_cfg = text.shape[0] == 2
-        for t in sch.timesteps:
+        for i, t in enumerate(sch.timesteps):
             x_in = torch.cat([latents] * 2) if do_cfg else latents
             x_in = sch.scale_model_input(x_in, t)
             eps = self.unet(x_in, t, encoder_hidden_states=text).sample
@@ -275,26 +370,30 @@ class AnimateDiffPipeline:
                 u, c = eps.chunk(2)
                 eps = u + guidance_scale * (c - u)
             latents = sch.step(eps, t, latents).prev_sample
+            if callback is not None:
+                ret = callback(self, i, t, {"latents": latents})
+                if isinstance(ret, dict) and ret.get("latents") is not None:
+                    latents = ret["latents"]
         return latents
 
     @torch.no_grad()
     def decode_latents(self, latents):
+        """latents [1,4,F,h,w] -> video [1,3,F,8h,8w] fp32 (AutoencoderKL decode on the b200ad kernels, vae.py)."""
         if self.vae is None:
             raise RuntimeError("pipeline was built without a VAE (with_vae=False); use output_type='latent'")
-        z = (latents / self.vae.scaling_factor)[0].permute(1, 0, 2, 3)          # [F, 4, h, w]
-        img = torch.cat([self.vae.decode(z[i:i + 16]) for i in range(0, z.shape[0], 16)])
-        return img[None].permute(0, 2, 1, 3, 4).float()                          # [1, 3, F, H, W]
+        return self.vae.decode_video(latents.float())
 
-    @staticmethod
-    def postprocess_video(video, output_type="pil"):
-        v = (video / 2 + 0.5).clamp(0, 1)
+    def postprocess_video(self, video, output_type="pil"):
+        """diffusers VideoProcessor.postprocess_video: (x/2+0.5).clamp(0,1) -> 'pt' [1,F,3,H,W] float, 'np'
+        [1,F,H,W,3] float, 'pil' list of lists of PIL images.  The uint8 conversion is b200ad_video_to_u8."""
+        u8 = get_ops("fp32").video_to_u8(video[0].float().contiguous())              # [F, H, W, 3] uint8 on the device
         if output_type == "pt":
-            return v.permute(0, 2, 1, 3, 4)
-        arr = (v.permute(0, 2, 3, 4, 1) * 255).round().to(torch.uint8).cpu().numpy()   # [1, F, H, W, 3]
+            return (u8.permute(0, 3, 1, 2).float() / 255.0)[None]
+        arr = u8.cpu().numpy()
         if output_type == "np":
-            return arr.astype(np.float32) / 255.0
+            return arr.astype(np.float32)[None] / 255.0
         from PIL import Image
-        return [[Image.fromarray(f) for f in vid] for vid in arr]
+        return [[Image.fromarray(f) for f in arr]]
 
     # ---- the call ------------------------------------------------------------------------------
     @torch.no_grad()
@@ -334,11 +433,14 @@ class AnimateDiffPipeline:
         fast = hasattr(self.scheduler, "step_coefficients")
         if not fast and not hasattr(self.scheduler, "set_timesteps"):
             raise TypeError("pipe.scheduler must be a scheduler object (assign DDIMScheduler.from_config(...))")
+        # diffusers order: set_timesteps BEFORE prepare_latents -- init_noise_sigma of EulerDiscreteScheduler
+        # ("leading" spacing) depends on the sigma table of THIS call's step count
+        self.scheduler.set_timesteps(num_inference_steps, **({} if fast else {"device": "cuda"}))
         lat = self.prepare_latents(num_frames, height, width, generator, latents)
         if fast:
             lat = self.denoise(lat, text, guidance_scale, num_inference_steps, callback_on_step_end)
         else:
-            lat = self._denoise_generic(lat, text, guidance_scale, num_inference_steps)
+            lat = self._denoise_generic(lat, text, guidance_scale, num_inference_steps, callback_on_step_end)
         self.last_latents = lat
         if output_type == "latent":
             out = lat.to(self.dtype).clone()

@@ -24,6 +24,8 @@ from typing import Dict, List, Optional, Tuple
 import torch
 import torch.nn as nn
 
+from . import leaf as _leaf
+from .leaf import Conv2d, GroupNorm, LayerNorm, Linear, SiLU
 from .ops import Ops, get_ops
 
 
@@ -51,6 +53,11 @@ class UNetMotionConfig:
 
 @dataclass
 class UNetMotionOutput:
+    sample: torch.Tensor
+
+
+@dataclass
+class Transformer2DModelOutput:
     sample: torch.Tensor
 
 
@@ -122,10 +129,10 @@ class Attention(_Packable):
         self.cross_attention_dim = cross_attention_dim
         self.is_cross_attention = cross_attention_dim is not None
         kv_dim = query_dim if cross_attention_dim is None else cross_attention_dim
-        self.to_q = nn.Linear(query_dim, query_dim, bias=False)
-        self.to_k = nn.Linear(kv_dim, query_dim, bias=False)
-        self.to_v = nn.Linear(kv_dim, query_dim, bias=False)
-        self.to_out = nn.ModuleList([nn.Linear(query_dim, query_dim, bias=True), nn.Dropout(0.0)])
+        self.to_q = Linear(query_dim, query_dim, bias=False)
+        self.to_k = Linear(kv_dim, query_dim, bias=False)
+        self.to_v = Linear(kv_dim, query_dim, bias=False)
+        self.to_out = nn.ModuleList([Linear(query_dim, query_dim, bias=True), nn.Dropout(0.0)])
         self.processor = None       # set by UNetMotionModel.set_attn_processor
 
     def _pack(self, o: Ops):
@@ -212,7 +219,14 @@ class Attention(_Packable):
 class GEGLU(nn.Module):
     def __init__(self, dim_in: int, dim_out: int):
         super().__init__()
-        self.proj = nn.Linear(dim_in, dim_out * 2)
+        self.proj = Linear(dim_in, dim_out * 2)
+
+    def forward(self, hidden_states, *a, **kw):
+        """Module mode: h, g = proj(x).chunk(2, -1); h * gelu(g) (exact erf GELU)."""
+        hg = self.proj(hidden_states)
+        o = get_ops(_mode_of(self))
+        out = o.geglu_gate(_leaf.rows_f32(hg))
+        return out.view(*hg.shape[:-1], hg.shape[-1] // 2).to(hidden_states.dtype)
 
 
 class FeedForward(_Packable):
@@ -220,7 +234,7 @@ class FeedForward(_Packable):
 
     def __init__(self, dim: int):
         super().__init__()
-        self.net = nn.ModuleList([GEGLU(dim, dim * 4), nn.Dropout(0.0), nn.Linear(dim * 4, dim)])
+        self.net = nn.ModuleList([GEGLU(dim, dim * 4), nn.Dropout(0.0), Linear(dim * 4, dim)])
 
     def _pack(self, o: Ops):
         w, b = self.net[0].proj.weight.detach(), self.net[0].proj.bias.detach()
@@ -230,6 +244,12 @@ class FeedForward(_Packable):
         bi = torch.stack([b[:half], b[half:]], 1).reshape(2 * half)
         return {"w1": _dev_w(o, wi), "b1": _dev_f(bi), "w2": _dev_w(o, self.net[2].weight),
                 "b2": _dev_f(self.net[2].bias)}
+
+    def forward(self, hidden_states, *a, **kw):
+        """Module mode (diffusers FeedForward.forward): GEGLU -> Dropout -> Linear."""
+        for m in self.net:
+            hidden_states = m(hidden_states)
+        return hidden_states
 
     def run(self, st: _State, n_op, h, *, op_only: bool):
         """h + ff(n): returns fp32 (in place) or, when the caller only needs an operand, the operand-typed sum."""
@@ -254,6 +274,11 @@ class SinusoidalPositionalEmbedding(nn.Module):
         pe[0, :, 1::2] = torch.cos(position * div_term)
         self.register_buffer("pe", pe)
 
+    def forward(self, x):
+        """Module mode: x [Bt, F, C] + pe[:, :F]."""
+        _, f, c = x.shape
+        return _leaf.add(get_ops(_mode_of(self)), x, self.pe[0, :f].to(x.device), div=1, mod=f * c)
+
 
 class BasicTransformerBlock(_Packable):
     """Spatial block (self-attn, text cross-attn, GEGLU FF) or temporal block (two self-attentions with
@@ -263,11 +288,11 @@ class BasicTransformerBlock(_Packable):
         super().__init__()
         self.temporal = temporal
         self.pos_embed = SinusoidalPositionalEmbedding(dim, max_seq) if temporal else None
-        self.norm1 = nn.LayerNorm(dim, eps=1e-5)
+        self.norm1 = LayerNorm(dim, eps=1e-5)
         self.attn1 = Attention(dim, heads)
-        self.norm2 = nn.LayerNorm(dim, eps=1e-5)
+        self.norm2 = LayerNorm(dim, eps=1e-5)
         self.attn2 = Attention(dim, heads, cross_attention_dim=None if temporal else cross_attention_dim)
-        self.norm3 = nn.LayerNorm(dim, eps=1e-5)
+        self.norm3 = LayerNorm(dim, eps=1e-5)
         self.ff = FeedForward(dim)
 
     def _pack(self, o: Ops):
@@ -277,9 +302,26 @@ class BasicTransformerBlock(_Packable):
         p["pe"] = _dev_f(self.pos_embed.pe[0]) if self.pos_embed is not None else None
         return p
 
-    def run(self, st: _State, h, nimg: int, hw: int):
-        """h: fp32 [nimg*hw, C] residual stream (updated in place).  Returns the operand-typed block output
-        (the only consumer is the proj_out GEMM)."""
+    def forward(self, hidden_states, attention_mask=None, encoder_hidden_states=None, encoder_attention_mask=None,
+                timestep=None, cross_attention_kwargs=None, class_labels=None, **kw):
+        """Module mode (diffusers BasicTransformerBlock.forward): every sub-module is called, so hooks fire."""
+        o = get_ops(_mode_of(self))
+        x = hidden_states
+        n = self.norm1(x)
+        if self.pos_embed is not None:
+            n = self.pos_embed(n)
+        x = _leaf.add(o, x, self.attn1(n, encoder_hidden_states=None, attention_mask=attention_mask))
+        n = self.norm2(x)
+        if self.pos_embed is not None:
+            n = self.pos_embed(n)
+        x = _leaf.add(o, x, self.attn2(n, encoder_hidden_states=None if self.temporal else encoder_hidden_states,
+                                       attention_mask=encoder_attention_mask))
+        return _leaf.add(o, x, self.ff(self.norm3(x)))
+
+    def run(self, st: _State, h, nimg: int, hw: int, last: bool = True):
+        """h: fp32 [nimg*hw, C] residual stream (updated in place).  last=True: returns the operand-typed block
+        output (its only consumer is the proj_out GEMM) and leaves h WITHOUT the feed-forward term; last=False
+        (another block follows): h += ff and h is returned."""
         o, p = st.o, self.packed(st.o)
         if self.temporal:
             n = o.layer_norm(h, p["g1"], p["b1"], self.norm1.eps, pe=p["pe"], hw=hw, frames=st.F)
@@ -292,7 +334,7 @@ class BasicTransformerBlock(_Packable):
             n = o.layer_norm(h, p["g2"], p["b2"], self.norm2.eps)
             self.attn2.run_cross(st, n, h, nimg, hw)
         n = o.layer_norm(h, p["g3"], p["b3"], self.norm3.eps)
-        return self.ff.run(st, n, h, op_only=True)
+        return self.ff.run(st, n, h, op_only=last)
 
 
 class Transformer2DModel(_Packable):
@@ -300,11 +342,11 @@ class Transformer2DModel(_Packable):
 
     def __init__(self, channels: int, heads: int, cross_attention_dim: int, groups: int = 32):
         super().__init__()
-        self.norm = nn.GroupNorm(groups, channels, eps=1e-6)
-        self.proj_in = nn.Conv2d(channels, channels, 1)
+        self.norm = GroupNorm(groups, channels, eps=1e-6)
+        self.proj_in = Conv2d(channels, channels, 1)
         self.transformer_blocks = nn.ModuleList(
             [BasicTransformerBlock(channels, heads, cross_attention_dim, temporal=False)])
-        self.proj_out = nn.Conv2d(channels, channels, 1)
+        self.proj_out = Conv2d(channels, channels, 1)
 
     def _pack(self, o: Ops):
         c = self.proj_in.weight.shape[0]
@@ -312,13 +354,28 @@ class Transformer2DModel(_Packable):
                 "win": _dev_w(o, self.proj_in.weight.reshape(c, c)), "bin": _dev_f(self.proj_in.bias),
                 "wout": _dev_w(o, self.proj_out.weight.reshape(c, c)), "bout": _dev_f(self.proj_out.bias)}
 
+    def forward(self, hidden_states, encoder_hidden_states=None, timestep=None, added_cond_kwargs=None,
+                class_labels=None, cross_attention_kwargs=None, attention_mask=None, encoder_attention_mask=None,
+                return_dict: bool = True):
+        """Module mode (diffusers Transformer2DModel.forward, use_linear_projection=False)."""
+        n, c, h, w = hidden_states.shape
+        residual = hidden_states
+        x = self.proj_in(self.norm(hidden_states))
+        x = x.permute(0, 2, 3, 1).reshape(n, h * w, c)
+        for blk in self.transformer_blocks:
+            x = blk(x, attention_mask=attention_mask, encoder_hidden_states=encoder_hidden_states,
+                    encoder_attention_mask=encoder_attention_mask, timestep=timestep)
+        x = x.reshape(n, h, w, c).permute(0, 3, 1, 2).contiguous()
+        out = _leaf.add(get_ops(_mode_of(self)), self.proj_out(x), residual)
+        return Transformer2DModelOutput(sample=out) if return_dict else (out,)
+
     def run(self, st: _State, x, nimg: int, hw: int):
         """x: fp32 [nimg*hw, C], updated in place (x += proj_out(block(proj_in(GN(x)))))."""
         o, p = st.o, self.packed(st.o)
         a = o.group_norm(x, None, nimg, hw, self.norm.num_groups, p["gn_g"], p["gn_b"], self.norm.eps, silu=False)
         h, _ = o.gemm(a, p["win"], bias=p["bin"], want_f32=True)
         for blk in self.transformer_blocks[:-1]:
-            blk.run(st, h, nimg, hw)
+            blk.run(st, h, nimg, hw, last=False)
         hb = self.transformer_blocks[-1].run(st, h, nimg, hw)
         o.gemm(hb, p["wout"], bias=p["bout"], residual=x, out_f32=x)
         return x
@@ -331,11 +388,11 @@ class AnimateDiffTransformer3D(_Packable):
 
     def __init__(self, channels: int, heads: int, groups: int = 32, max_seq: int = 32):
         super().__init__()
-        self.norm = nn.GroupNorm(groups, channels, eps=1e-6)
-        self.proj_in = nn.Linear(channels, channels)
+        self.norm = GroupNorm(groups, channels, eps=1e-6)
+        self.proj_in = Linear(channels, channels)
         self.transformer_blocks = nn.ModuleList(
             [BasicTransformerBlock(channels, heads, None, temporal=True, max_seq=max_seq)])
-        self.proj_out = nn.Linear(channels, channels)
+        self.proj_out = Linear(channels, channels)
 
     def _pack(self, o: Ops):
         return {"gn_g": _dev_f(self.norm.weight), "gn_b": _dev_f(self.norm.bias),
@@ -349,18 +406,28 @@ class AnimateDiffTransformer3D(_Packable):
                          frames_per_stat=st.F)
         h, _ = o.gemm(a, p["win"], bias=p["bin"], want_f32=True)
         for blk in self.transformer_blocks[:-1]:
-            blk.run(st, h, nimg, hw)
+            blk.run(st, h, nimg, hw, last=False)
         hb = self.transformer_blocks[-1].run(st, h, nimg, hw)
         o.gemm(hb, p["wout"], bias=p["bout"], residual=x, out_f32=x)
         return x
 
-    def forward(self, hidden_states, encoder_hidden_states=None, timestep=None, num_frames: int = 1, **kw):
-        """Module mode: [B*F, C, h, w] -> same (used by /root/reference/experiments/03_trace_forward_pass.py:182-205)."""
-        bf, c, hh, ww = hidden_states.shape
-        st = _State(get_ops(_mode_of(self)), bf // num_frames, num_frames)
-        x = _to_rows(hidden_states)
-        x = self.run(st, x, hh * ww)
-        return _from_rows(x, bf, hh, ww, hidden_states.dtype)
+    def forward(self, hidden_states, encoder_hidden_states=None, timestep=None, class_labels=None,
+                num_frames: int = 1, cross_attention_kwargs=None, **kw):
+        """Module mode (diffusers AnimateDiffTransformer3D.forward): [B*F, C, h, w] -> same, through the sub-modules with
+        diffusers' tensor shapes -- the temporal attention sees [B*h*w, F, C]
+        (/root/reference/experiments/03_trace_forward_pass.py:160-169,182-205; docs/02_video_diffusion_architecture.md:69-81)."""
+        bf, c, h, w = hidden_states.shape
+        b = bf // num_frames
+        residual = hidden_states
+        x = hidden_states[None, :].reshape(b, num_frames, c, h, w).permute(0, 2, 1, 3, 4)
+        x = self.norm(x)
+        x = x.permute(0, 3, 4, 2, 1).reshape(b * h * w, num_frames, c)
+        x = self.proj_in(x)
+        for blk in self.transformer_blocks:
+            x = blk(x, encoder_hidden_states=encoder_hidden_states, timestep=timestep)
+        x = self.proj_out(x)
+        x = x[None, None, :].reshape(b, h, w, num_frames, c).permute(0, 3, 4, 1, 2).reshape(bf, c, h, w).contiguous()
+        return _leaf.add(get_ops(_mode_of(self)), x, residual)
 
 
 # ----------------------------------------------------------------------------- layout helpers (module mode)
@@ -392,14 +459,14 @@ class ResnetBlock2D(_Packable):
     def __init__(self, cin: int, cout: int, temb_dim: int, groups: int = 32, eps: float = 1e-5):
         super().__init__()
         self.in_channels, self.out_channels = cin, cout
-        self.norm1 = nn.GroupNorm(groups, cin, eps=eps)
-        self.conv1 = nn.Conv2d(cin, cout, 3, padding=1)
-        self.time_emb_proj = nn.Linear(temb_dim, cout)
-        self.norm2 = nn.GroupNorm(groups, cout, eps=eps)
+        self.norm1 = GroupNorm(groups, cin, eps=eps)
+        self.conv1 = Conv2d(cin, cout, 3, padding=1)
+        self.time_emb_proj = Linear(temb_dim, cout)
+        self.norm2 = GroupNorm(groups, cout, eps=eps)
         self.dropout = nn.Dropout(0.0)
-        self.conv2 = nn.Conv2d(cout, cout, 3, padding=1)
-        self.nonlinearity = nn.SiLU()
-        self.conv_shortcut = nn.Conv2d(cin, cout, 1) if cin != cout else None
+        self.conv2 = Conv2d(cout, cout, 3, padding=1)
+        self.nonlinearity = SiLU()
+        self.conv_shortcut = Conv2d(cin, cout, 1) if cin != cout else None
         self._temb_off = None       # column offset into the step's fused time_emb_proj output
 
     def _pack(self, o: Ops):
@@ -434,14 +501,16 @@ class ResnetBlock2D(_Packable):
         out, _ = o.conv3x3(a2, p["w2"], nimg, h, w, bias=p["cb2"], residual=res)
         return out
 
-    def forward(self, input_tensor, temb, **kw):
-        """Module mode: NCHW in/out, temb [N, 1280] (already repeated per frame, as diffusers passes it)."""
-        n, c, hh, ww = input_tensor.shape
+    def forward(self, input_tensor, temb, *a, **kw):
+        """Module mode (diffusers ResnetBlock2D.forward): NCHW in/out, temb [N, 1280] (repeated per frame)."""
         o = get_ops(_mode_of(self))
-        st = _State(o, n, 1)
-        tp = _rows_linear_f32(o, temb, self.time_emb_proj)
-        out = self.run(st, _to_rows(input_tensor), None, n, hh, ww, temb_proj=tp)
-        return _from_rows(out, n, hh, ww, input_tensor.dtype)
+        n, _, hh, ww = input_tensor.shape
+        h = self.conv1(self.nonlinearity(self.norm1(input_tensor)))
+        t = self.time_emb_proj(self.nonlinearity(temb))                     # [N, cout]
+        h = _leaf.add(o, h, t, div=hh * ww, mod=t.numel())                  # h + t[:, :, None, None]
+        h = self.conv2(self.dropout(self.nonlinearity(self.norm2(h))))
+        x = input_tensor if self.conv_shortcut is None else self.conv_shortcut(input_tensor)
+        return _leaf.add(o, x, h)
 
 
 def _rows_linear_f32(o: Ops, temb, lin: nn.Linear):
@@ -456,10 +525,13 @@ class Downsample2D(_Packable):
 
     def __init__(self, channels: int):
         super().__init__()
-        self.conv = nn.Conv2d(channels, channels, 3, stride=2, padding=1)
+        self.conv = Conv2d(channels, channels, 3, stride=2, padding=1)
 
     def _pack(self, o: Ops):
         return {"w": _pack_conv3x3(o, self.conv.weight), "b": _dev_f(self.conv.bias)}
+
+    def forward(self, hidden_states, *a, **kw):
+        return self.conv(hidden_states)
 
     def run(self, st: _State, x, nimg: int, h: int, w: int):
         o, p = st.o, self.packed(st.o)
@@ -473,10 +545,17 @@ class Upsample2D(_Packable):
 
     def __init__(self, channels: int):
         super().__init__()
-        self.conv = nn.Conv2d(channels, channels, 3, padding=1)
+        self.conv = Conv2d(channels, channels, 3, padding=1)
 
     def _pack(self, o: Ops):
         return {"w": _pack_conv3x3(o, self.conv.weight), "b": _dev_f(self.conv.bias)}
+
+    def forward(self, hidden_states, output_size=None, *a, **kw):
+        """Module mode: F.interpolate(scale_factor=2, mode="nearest") (b200ad_cast mode 2) then the conv."""
+        n, c, h, w = hidden_states.shape
+        o = get_ops("fp32")
+        up = o.cast(_leaf.nchw_to_rows(hidden_states), n, h, w, c, mode=2)
+        return self.conv(_leaf.rows_to_nchw(up, n, 2 * h, 2 * w, hidden_states.dtype))
 
     def run(self, st: _State, x, nimg: int, h: int, w: int):
         o, p = st.o, self.packed(st.o)
@@ -503,6 +582,22 @@ class DownBlockMotion(nn.Module):
             self.motion_modules.append(AnimateDiffTransformer3D(cout, cfg.motion_num_attention_heads,
                                                                 cfg.motion_norm_num_groups, cfg.motion_max_seq_length))
         self.downsamplers = nn.ModuleList([Downsample2D(cout)]) if add_downsample else None
+
+    def forward(self, hidden_states, temb=None, encoder_hidden_states=None, attention_mask=None, num_frames: int = 1,
+                encoder_attention_mask=None, cross_attention_kwargs=None, additional_residuals=None, **kw):
+        """Module mode (diffusers [CrossAttn]DownBlockMotion.forward) -> (hidden_states, output_states)."""
+        x, outs = hidden_states, ()
+        for i, res in enumerate(self.resnets):
+            x = res(x, temb)
+            if self.has_cross_attention:
+                x = self.attentions[i](x, encoder_hidden_states=encoder_hidden_states, return_dict=False)[0]
+            x = self.motion_modules[i](x, num_frames=num_frames)
+            outs += (x,)
+        if self.downsamplers is not None:
+            for d in self.downsamplers:
+                x = d(x)
+            outs += (x,)
+        return x, outs
 
     def run(self, st: _State, x, h: int, w: int):
         nimg = st.B * st.F
@@ -536,6 +631,14 @@ class UNetMidBlockCrossAttnMotion(nn.Module):
                                                                       cfg.motion_norm_num_groups,
                                                                       cfg.motion_max_seq_length)])
 
+    def forward(self, hidden_states, temb=None, encoder_hidden_states=None, attention_mask=None,
+                cross_attention_kwargs=None, encoder_attention_mask=None, num_frames: int = 1, **kw):
+        """Module mode (diffusers UNetMidBlockCrossAttnMotion.forward)."""
+        x = self.resnets[0](hidden_states, temb)
+        x = self.attentions[0](x, encoder_hidden_states=encoder_hidden_states, return_dict=False)[0]
+        x = self.motion_modules[0](x, num_frames=num_frames)
+        return self.resnets[1](x, temb)
+
     def run(self, st: _State, x, h: int, w: int):
         nimg = st.B * st.F
         x = self.resnets[0].run(st, x, None, nimg, h, w)
@@ -564,6 +667,23 @@ class UpBlockMotion(nn.Module):
                                                                 cfg.motion_norm_num_groups, cfg.motion_max_seq_length))
         self.upsamplers = nn.ModuleList([Upsample2D(out_c)]) if add_upsample else None
 
+    def forward(self, hidden_states, res_hidden_states_tuple, temb=None, encoder_hidden_states=None,
+                upsample_size=None, attention_mask=None, encoder_attention_mask=None, cross_attention_kwargs=None,
+                num_frames: int = 1, **kw):
+        """Module mode (diffusers [CrossAttn]UpBlockMotion.forward): skips are popped from the END of the tuple."""
+        x = hidden_states
+        for i, res in enumerate(self.resnets):
+            skip = res_hidden_states_tuple[-1]
+            res_hidden_states_tuple = res_hidden_states_tuple[:-1]
+            x = res(torch.cat([x, skip], dim=1), temb)
+            if self.has_cross_attention:
+                x = self.attentions[i](x, encoder_hidden_states=encoder_hidden_states, return_dict=False)[0]
+            x = self.motion_modules[i](x, num_frames=num_frames)
+        if self.upsamplers is not None:
+            for u in self.upsamplers:
+                x = u(x, upsample_size)
+        return x
+
     def run(self, st: _State, x, skips: list, h: int, w: int):
         nimg = st.B * st.F
         for i, res in enumerate(self.resnets):
@@ -586,13 +706,21 @@ class Timesteps(nn.Module):
         super().__init__()
         self.num_channels = dim
 
+    def forward(self, timesteps):
+        """Module mode: sinusoid(dim), flip_sin_to_cos=True, freq_shift=0 -> fp32 [B, dim]."""
+        t = timesteps.to(device="cuda", dtype=torch.float32).reshape(-1).contiguous()
+        return get_ops("fp32").timestep_sinusoid(t, self.num_channels)
+
 
 class TimestepEmbedding(nn.Module):
     def __init__(self, cin: int, dim: int):
         super().__init__()
-        self.linear_1 = nn.Linear(cin, dim)
-        self.act = nn.SiLU()
-        self.linear_2 = nn.Linear(dim, dim)
+        self.linear_1 = Linear(cin, dim)
+        self.act = SiLU()
+        self.linear_2 = Linear(dim, dim)
+
+    def forward(self, sample, condition=None):
+        return self.linear_2(self.act(self.linear_1(sample)))
 
 
 # ----------------------------------------------------------------------------- the UNet
@@ -608,7 +736,7 @@ class UNetMotionModel(_Packable):
         self.cfg = cfg
         self.config = cfg
         boc = cfg.block_out_channels
-        self.conv_in = nn.Conv2d(cfg.in_channels, boc[0], 3, padding=1)
+        self.conv_in = Conv2d(cfg.in_channels, boc[0], 3, padding=1)
         self.time_proj = Timesteps(boc[0])
         self.time_embedding = TimestepEmbedding(boc[0], cfg.time_embed_dim)
 
@@ -633,9 +761,9 @@ class UNetMotionModel(_Packable):
             cls = CrossAttnUpBlockMotion if rev_cross[i] else UpBlockMotion
             self.up_blocks.append(cls(cfg, prev, oc, scs, rev_cross[i], add_upsample=not last))
             prev = oc
-        self.conv_norm_out = nn.GroupNorm(cfg.norm_num_groups, boc[0], eps=cfg.norm_eps)
-        self.conv_act = nn.SiLU()
-        self.conv_out = nn.Conv2d(boc[0], cfg.out_channels, 3, padding=1)
+        self.conv_norm_out = GroupNorm(cfg.norm_num_groups, boc[0], eps=cfg.norm_eps)
+        self.conv_act = SiLU()
+        self.conv_out = Conv2d(boc[0], cfg.out_channels, 3, padding=1)
         self.set_mode(mode)
         for p in self.parameters():
             p.requires_grad_(False)
@@ -762,10 +890,56 @@ class UNetMotionModel(_Packable):
         res["rows"] = e2.shape[0]
         return res
 
+    # ---- module mode ------------------------------------------------------------------------------
+    module_mode = False          # True: always run through the sub-modules (diffusers' eager structure)
+
+    def _hooks_registered(self) -> bool:
+        """True when any SUB-module carries a forward (pre-)hook: the fused plan never calls sub-modules, so a
+        tracer (/root/reference/utils/forward_tracer.py:177-194) would see nothing."""
+        import torch.nn.modules.module as _m
+        if _m._global_forward_hooks or _m._global_forward_pre_hooks:
+            return True
+        for m in self.modules():
+            if m is not self and (m._forward_hooks or m._forward_pre_hooks):
+                return True
+        return False
+
+    @torch.no_grad()
+    def _forward_modules(self, sample, timestep, encoder_hidden_states):
+        """diffusers' UNetMotionModel.forward, module by module: every sub-module is invoked
+        through ``module(...)`` with diffusers' tensor shapes, each running its own libb200ad kernel (leaf.py)."""
+        B, _, F, h, w = sample.shape
+        t = self._timestep_tensor(timestep, B)
+        emb = self.time_embedding(self.time_proj(t).to(sample.dtype))
+        emb = emb.repeat_interleave(F, dim=0)
+        ctx = encoder_hidden_states.to(sample.dtype)
+        if ctx.shape[0] == B:
+            ctx = ctx.repeat_interleave(F, dim=0)
+        elif ctx.shape[0] != B * F:
+            raise ValueError(f"encoder_hidden_states batch {ctx.shape[0]} is neither B={B} nor B*F={B * F}")
+        x = sample.permute(0, 2, 1, 3, 4).reshape(B * F, -1, h, w)
+        x = self.conv_in(x)
+        skips = (x,)
+        for blk in self.down_blocks:
+            x, s = blk(x, temb=emb, encoder_hidden_states=ctx, num_frames=F)
+            skips += s
+        x = self.mid_block(x, temb=emb, encoder_hidden_states=ctx, num_frames=F)
+        for blk in self.up_blocks:
+            n = len(blk.resnets)
+            x = blk(x, skips[-n:], temb=emb, encoder_hidden_states=ctx, num_frames=F)
+            skips = skips[:-n]
+        x = self.conv_out(self.conv_act(self.conv_norm_out(x)))
+        x = x[None, :].reshape(B, F, -1, h, w).permute(0, 2, 1, 3, 4)
+        return UNetMotionOutput(sample=x.contiguous())
+
     @torch.no_grad()
     def forward(self, sample, timestep, encoder_hidden_states, text_kv=None, **kw):
         if not sample.is_cuda:
             raise RuntimeError("UNetMotionModel: CUDA tensors required (the b200ad path has no CPU fallback)")
+        if sample.shape[2] > self.cfg.motion_max_seq_length:
+            raise ValueError(f"num_frames={sample.shape[2]} exceeds motion_max_seq_length={self.cfg.motion_max_seq_length}")
+        if text_kv is None and (self.module_mode or self._hooks_registered()):
+            return self._forward_modules(sample, timestep, encoder_hidden_states)
         o = get_ops(self.mode)
         P = self.packed(o)
         B, cin, F, h, w = sample.shape
