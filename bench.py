@@ -186,40 +186,6 @@ def run_reference_arm(args):
 
 
 # ----------------------------------------------------------------------------- our arm
-def _teardown_process_group(pipe, ok: bool):
-    """Multi-rank exit.  The captured CUDA graphs hold the pair communicator (the per-step all-gather is inside the
-    graph), so they are reset first; then the device is drained, the ranks meet, and the process group is destroyed
-    under a watchdog (a wedged NCCL finalizer must not keep torchrun alive).  A failing rank leaves with a non-zero
-    exit code."""
-    import gc
-    import torch
-    import torch.distributed as dist
-    for pl in list(pipe._plans.values()):
-        if pl.graph is not None:
-            pl.graph.reset()
-            pl.graph = None
-    pipe._plans.clear()
-    gc.collect()
-    torch.cuda.synchronize()
-    code = 0 if ok else 1
-
-    def _bail():
-        sys.stdout.flush()
-        sys.stderr.flush()
-        os._exit(code)
-
-    wd = threading.Timer(60.0, _bail)
-    wd.daemon = True
-    wd.start()
-    try:
-        dist.barrier()
-        torch.cuda.synchronize()
-        dist.destroy_process_group()
-    finally:
-        wd.cancel()
-    return code
-
-
 def run_b200_arm(args):
     import torch
     import torch.distributed as dist
@@ -266,7 +232,8 @@ def run_b200_arm(args):
         if world == 1:
             raise
     if world > 1:
-        return _teardown_process_group(pipe, ok) if pipe is not None else 1
+        from b200ad.dist_util import teardown_process_group
+        return teardown_process_group(pipe, ok)
     return 0 if ok else 1
 
 

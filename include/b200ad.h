@@ -70,10 +70,32 @@ int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const float* x1, int 
                     const float* partial, int frames_per_stat, float eps, const float* gamma, const float* beta,
                     int silu, void* out_op, void* raw_op, void* stream);
 
+/* diagnostics: how many of the GroupNorm ticket counters are non-zero (must be 0 between calls); synchronises. */
+int b200ad_gn_counters_nonzero(void);
+
 /* Statistics + apply in one call (same arguments and workspace as the pair above). */
 int b200ad_group_norm(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
                       float* partial, int frames_per_stat, float eps, const float* gamma, const float* beta, int silu,
                       void* out_op, void* raw_op, void* stream);
+
+/* ---- K6 without the statistics pass: the producing GEMM / conv emits per-(32-row slot, column) sums of its fp32
+ * output from its epilogue (b200ad_gemm_stats / b200ad_conv3x3_stats: float2 col_stats[(image*spi + k)*N + col], spi =
+ * b200ad_stats_slots(conv, h, w) slots per image), and b200ad_gn_apply_stats reduces them (tiny) and applies: the
+ * GroupNorm reads its input ONCE.  meanrstd_ws: (nimg/frames_per_stat)*groups float2 of workspace.  Same module
+ * replacements as K6 / K1 / K2; the stats entry points write the fp32 output only. */
+int b200ad_stats_slots(int conv, int h, int w);
+int b200ad_gemm_stats(int op_dtype, const void* A, long long lda, const void* W, int M, int N, int K,
+                      const float* bias, const float* row_bias, int rb_div, int ld_rb, const float* residual,
+                      long long ld_res, float* out_f32, long long ld_o32, float* col_stats, int rows_per_image,
+                      void* stream);
+int b200ad_conv3x3_stats(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout,
+                         int mode, const float* bias, const float* row_bias, int rb_div, int ld_rb,
+                         const float* residual, long long ld_res, float* out_f32, long long ld_o32, float* col_stats,
+                         void* stream);
+int b200ad_gn_apply_stats(int op_dtype, const float* x0, int c0, const float* st0, int spi0, const float* x1, int c1,
+                          const float* st1, int spi1, int nimg, int hw, int groups, int frames_per_stat, float eps,
+                          const float* gamma, const float* beta, int silu, float* meanrstd_ws, void* out_op,
+                          void* raw_op, void* stream);
 
 /* ---- K7: LayerNorm (+ sinusoidal positional-embedding add of the motion module; replaces nn.LayerNorm and
  * SinusoidalPositionalEmbedding).  x fp32 [rows,C]; pe fp32 [max_seq,C] or NULL; frame index of a row is

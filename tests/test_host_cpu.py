@@ -157,3 +157,90 @@ def test_diffusers_shim_import_surface():
         sys.path.remove(os.path.join(ROOT, "compat"))
         for k in [k for k in sys.modules if k == "diffusers" or k.startswith("diffusers.")]:
             del sys.modules[k]
+
+
+def test_euler_init_noise_sigma_follows_the_current_schedule():
+    """with SD1.5's own scheduler config (timestep_spacing='leading', steps_offset=1) Euler's
+    init_noise_sigma depends on THIS call's sigma table, so the pipeline sets the timesteps before it draws / scales the
+    latents (diffusers' order).  Known answers: 14.6488 before set_timesteps, 11.7188 at 25 steps."""
+    from b200ad.schedulers import EulerDiscreteScheduler, SD15_SCHEDULER_CONFIG
+    from oracle.schedulers import OracleEuler
+    s = EulerDiscreteScheduler.from_config(SD15_SCHEDULER_CONFIG)
+    assert abs(s.init_noise_sigma - 14.6488) < 1e-3
+    for n in (25, 15, 25):                                   # consecutive calls with different step counts
+        s.set_timesteps(n)
+        o = OracleEuler(beta_schedule="scaled_linear", timestep_spacing="leading", steps_offset=1)
+        o.set_timesteps(n)
+        assert abs(s.init_noise_sigma - o.init_noise_sigma) < 1e-6
+        assert abs(s.first_in_scale() - 1.0 / (float(o.sigmas[0]) ** 2 + 1) ** 0.5) < 1e-7
+    s.set_timesteps(25)
+    assert abs(s.init_noise_sigma - 11.7188) < 1e-3
+    for sp in ("linspace", "trailing"):
+        e = EulerDiscreteScheduler.from_config(SD15_SCHEDULER_CONFIG, timestep_spacing=sp)
+        e.set_timesteps(25)
+        assert abs(e.init_noise_sigma - float(e.sigmas.max())) < 1e-7
+    import inspect
+    from b200ad import pipeline
+    src = inspect.getsource(pipeline.AnimateDiffPipeline.__call__)
+    assert src.index("set_timesteps") < src.index("prepare_latents")
+
+
+def test_checkpoint_loading_refuses_silent_partial_loads(tmp_path):
+    """a key mismatch must raise instead of leaving seeded-random weights in place; SD1.5's legacy VAE
+    attention names (query/key/value/proj_attn) are renamed on load."""
+    import torch.nn as nn
+    from b200ad.pipeline import _load_checked, _rename_legacy_vae_keys
+    m = nn.Sequential(nn.Linear(4, 4), nn.Linear(4, 4))
+    sd = m.state_dict()
+    _load_checked(m, sd, "ok")
+    bad = {k: v for k, v in sd.items() if not k.startswith("1.")}
+    with pytest.raises(RuntimeError, match="missing"):
+        _load_checked(m, bad, "partial")
+    _load_checked(m, bad, "allowed", allow_missing=lambda k: k.startswith("1."))
+    with pytest.raises(RuntimeError, match="unexpected"):
+        _load_checked(m, {**sd, "2.weight": torch.zeros(1)}, "extra")
+    legacy = {"decoder.mid_block.attentions.0.query.weight": torch.zeros(8, 8, 1, 1),
+              "decoder.mid_block.attentions.0.proj_attn.bias": torch.zeros(8),
+              "decoder.mid_block.attentions.0.group_norm.weight": torch.zeros(8)}
+    out = _rename_legacy_vae_keys(legacy)
+    assert set(out) == {"decoder.mid_block.attentions.0.to_q.weight", "decoder.mid_block.attentions.0.to_out.0.bias",
+                        "decoder.mid_block.attentions.0.group_norm.weight"}
+    assert out["decoder.mid_block.attentions.0.to_q.weight"].shape == (8, 8)
+
+
+def test_denoise_plan_table_is_keyed_on_scheduler_config_contents():
+    import inspect
+    from b200ad import pipeline
+    src = inspect.getsource(pipeline.DenoisePlan.load)
+    assert "id(scheduler)" not in src and "scheduler.config" in src
+
+
+def test_vae_state_dict_follows_diffusers_names():
+    from b200ad.vae import AutoencoderKLDecoder
+    from oracle.vae import make_oracle_vae
+    with torch.device("meta"):
+        v = AutoencoderKLDecoder()
+    keys = set(v.state_dict())
+    for k in ("post_quant_conv.weight", "decoder.conv_in.weight", "decoder.mid_block.attentions.0.to_q.bias",
+              "decoder.mid_block.attentions.0.to_out.0.weight", "decoder.mid_block.resnets.1.conv2.weight",
+              "decoder.up_blocks.0.upsamplers.0.conv.weight", "decoder.up_blocks.2.resnets.0.conv_shortcut.weight",
+              "decoder.up_blocks.3.resnets.2.norm2.bias", "decoder.conv_norm_out.weight", "decoder.conv_out.bias"):
+        assert k in keys, k
+    assert keys == set(make_oracle_vae(up_channels=(512, 512, 256, 128)).state_dict())
+    n = sum(p.numel() for p in v.parameters())
+    assert n == 49_490_199, n            # SD1.5 AutoencoderKL decoder + post_quant_conv
+
+
+def test_sweep_exporter_writes_the_reference_layout(tmp_path):
+    """FrameExporter (row f3) in its synchronous form: frames/frame_%04d.png, <id>.gif, config.json last (05:172-190)."""
+    import numpy as np
+    from b200ad import sweep
+    run = sweep.sweep_runs(video_filter="portrait", phase="cfg")[0]
+    arr = (np.random.default_rng(0).random((3, 16, 16, 3)) * 255).astype(np.uint8)
+    exp = tmp_path / run.experiment_id
+    (exp / "frames").mkdir(parents=True)
+    sweep._encode_run(arr, run, exp)
+    assert sorted(p.name for p in (exp / "frames").iterdir()) == [f"frame_{i:04d}.png" for i in range(3)]
+    assert (exp / f"{run.experiment_id}.gif").exists() and sweep.is_done(run, tmp_path)
+    from PIL import Image
+    assert np.array_equal(np.asarray(Image.open(exp / "frames" / "frame_0001.png")), arr[1])

@@ -146,6 +146,82 @@ def test_group_norm(mode, tol, nimg, hw, c0, c1, fps, silu):
     assert rel(raw.cpu(), x) < (4e-3 if mode == "bf16" else 1e-7)
 
 
+@pytest.mark.parametrize("nimg,h,w,cin,cout,fps", [(4, 16, 16, 64, 320, 1), (6, 8, 8, 64, 128, 1), (8, 8, 8, 128, 320, 4),
+                                                   (3, 12, 12, 64, 64, 1), (2, 24, 40, 64, 128, 1), (4, 32, 32, 64, 640, 2),
+                                                   (5, 8, 8, 64, 64, 1), (2, 64, 64, 64, 320, 1)])
+def test_group_norm_from_conv_epilogue_statistics(nimg, h, w, cin, cout, fps):
+    """GroupNorm whose statistics come from the producing conv's epilogue (b200ad_conv3x3_stats ->
+    b200ad_gn_apply_stats): the GroupNorm reads its input once.  Geometries: several images per tile (8x8), boxes that
+    overhang the image (12x12 rows, 24x40), an image count that does not fill the last tile, per-video statistics."""
+    o = ops("bf16")
+    x = bf(rnd(nimg, h, w, cin, seed=1))
+    wt = bf(rnd(cout, cin, 3, 3, seed=2, scale=(9 * cin) ** -0.5))
+    b = rnd(cout, seed=3) + 0.7
+    res = rnd(nimg * h * w, cout, seed=4)
+    conv = _conv_ref(x, wt, b).reshape(nimg * h * w, cout) + res
+    gamma, beta = rnd(cout, seed=5), rnd(cout, seed=6)
+    xr = conv.view(nimg // fps, fps * h * w, cout).permute(0, 2, 1)
+    ref = F.silu(F.group_norm(xr, 32, gamma, beta, eps=1e-5).permute(0, 2, 1).reshape(nimg * h * w, cout))
+    out32, _ = o.conv3x3(x.to(DEV, o.op_dtype), _pack_conv(wt).to(DEV, o.op_dtype), nimg, h, w, bias=b.to(DEV),
+                         residual=res.to(DEV), stats=True)
+    assert rel(out32.cpu(), conv) < 2e-5
+    supported = o._stats_ok(True, h, w) > 0          # a tile must hold >= 32 pixels of one image (not 12x12: 4x4 boxes)
+    assert (out32.data_ptr() in o.colstats) == supported, "column statistics emitted / not emitted unexpectedly"
+    assert supported or (h, w) == (12, 12)
+    n0 = lib_launches()
+    out = o.group_norm(out32, None, nimg, h * w, 32, gamma.to(DEV), beta.to(DEV), 1e-5, silu=True, frames_per_stat=fps)
+    if supported:
+        assert lib_launches() - n0 == 2                                  # finalize (tiny) + apply: no statistics pass
+        st, spi = o.colstats[out32.data_ptr()][:2]
+        tot = st.view(nimg, spi, cout, 2).sum(1).cpu()                   # per (image, channel) sum / sum of squares
+        per_img = conv.view(nimg, h * w, cout)
+        assert (tot[..., 0] - per_img.sum(1)).abs().max() < 2e-3 * (h * w) ** 0.5
+        assert rel(tot[..., 1], (per_img ** 2).sum(1)) < 1e-5
+    assert rel(out.cpu(), ref) < 4e-3
+    # the same tensor through the two-pass path gives the same answer
+    o.colstats.clear()
+    out2 = o.group_norm(out32, None, nimg, h * w, 32, gamma.to(DEV), beta.to(DEV), 1e-5, silu=True, frames_per_stat=fps)
+    assert rel(out.float(), out2.float()) < 2e-3
+
+
+@pytest.mark.parametrize("nimg,hw,c0,c1,K", [(4, 256, 320, 0, 320), (2, 1024, 640, 320, 64), (8, 64, 1280, 640, 128),
+                                             (16, 32, 320, 320, 64), (3, 4096, 320, 0, 64)])
+def test_group_norm_from_gemm_epilogue_statistics_concat(nimg, hw, c0, c1, K):
+    """Dense GEMM producers (proj_out of the transformers) and the UNet's skip concat: two tensors, each with its own
+    epilogue statistics, normalised as one channel-concatenated input (group boundaries may straddle the two)."""
+    o = ops("bf16")
+    M = nimg * hw
+    srcs = []
+    for i, c in enumerate((c0, c1)):
+        if not c:
+            srcs.append((None, None))
+            continue
+        a, w = bf(rnd(M, K, seed=10 + i)), bf(rnd(c, K, seed=20 + i, scale=K ** -0.5))
+        bias, res = rnd(c, seed=30 + i), rnd(M, c, seed=40 + i) * 2
+        x = res.to(DEV)
+        o.gemm(a.to(DEV, o.op_dtype), w.to(DEV, o.op_dtype), bias=bias.to(DEV), residual=x, out_f32=x, stats_hw=hw)
+        assert x.data_ptr() in o.colstats
+        srcs.append((x, a @ w.t() + bias + res))
+    C = c0 + c1
+    full = srcs[0][1] if not c1 else torch.cat([srcs[0][1], srcs[1][1]], -1)
+    gamma, beta = rnd(C, seed=3), rnd(C, seed=4)
+    ref = F.group_norm(full.view(nimg, hw, C).permute(0, 2, 1), 32, gamma, beta, eps=1e-6).permute(0, 2, 1).reshape(M, C)
+    n0 = lib_launches()
+    out, raw = o.group_norm(srcs[0][0], srcs[1][0], nimg, hw, 32, gamma.to(DEV), beta.to(DEV), 1e-6, silu=False,
+                            want_raw=True)
+    assert lib_launches() - n0 == 2
+    assert rel(out.cpu(), ref) < 4e-3 and rel(raw.cpu(), full) < 4e-3
+    # an in-place writer WITHOUT statistics invalidates the entry: the next GroupNorm takes the two-pass path
+    x0 = srcs[0][0]
+    o.gemm(bf(rnd(M, K, seed=50)).to(DEV, o.op_dtype), bf(rnd(c0, K, seed=51)).to(DEV, o.op_dtype), residual=x0, out_f32=x0)
+    assert x0.data_ptr() not in o.colstats
+
+
+def lib_launches():
+    from b200ad import lib
+    return lib.launch_count()
+
+
 @pytest.mark.parametrize("mode,tol", MODES)
 @pytest.mark.parametrize("rows,C,pe", [(1000, 320, False), (2 * 4 * 50, 640, True), (333, 1280, True), (64, 64, False)])
 def test_layer_norm(mode, tol, rows, C, pe):

@@ -115,8 +115,17 @@ def norm():
         g, b = torch.randn(C, device="cuda"), torch.randn(C, device="cuda")
         us = timeit(lambda: o.layer_norm(x, g, b))
         report(f"layernorm rows={32 * hw} C={C}", us, 0, x.numel() * 6.0)
+        o.colstats.clear()
         us = timeit(lambda: o.group_norm(x, None, 32, hw, 32, g, b, 1e-5, silu=True))
         report(f"groupnorm(stats+apply) n=32 hw={hw} C={C}", us, 0, x.numel() * 6.0)
+        # statistics from the producer's epilogue: a GEMM writes x (+ column sums), then finalize + apply only
+        a, w = bf(32 * hw, 64), bf(C, 64, scale=0.125)
+        o.gemm(a, w, residual=x, out_f32=x, stats_hw=hw)
+        us = timeit(lambda: o.group_norm(x, None, 32, hw, 32, g, b, 1e-5, silu=True))
+        report(f"groupnorm(epilogue stats: finalize+apply) n=32 hw={hw} C={C}", us, 0, x.numel() * 6.0)
+        us0 = timeit(lambda: o.gemm(a, w, residual=x, out_f32=x))
+        us1 = timeit(lambda: o.gemm(a, w, residual=x, out_f32=x, stats_hw=hw))
+        print(f"   producer GEMM (K=64) without / with column statistics: {us0:.1f} / {us1:.1f} us", flush=True)
 
 
 if __name__ == "__main__":

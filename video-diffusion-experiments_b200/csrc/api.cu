@@ -48,6 +48,8 @@ static void fill_epilogue(Epilogue& e, const float* bias, const float* row_bias,
   e.out_op = out_op;
   e.ld_oop = ld_oop;
   e.geglu = geglu;
+  e.col_stats = nullptr;
+  e.stats_hw = 0;
 }
 
 }  // namespace b200ad
@@ -67,25 +69,69 @@ const char* b200ad_last_error(void) { return g_err; }
 int b200ad_version(void) { return 100; }
 long long b200ad_launch_count(void) { return g_launches.load(); }
 
-int b200ad_gemm(int op_dtype, const void* A, long long lda, const void* W, int M, int N, int K, const float* bias,
-                const float* row_bias, int rb_div, int ld_rb, const float* residual, long long ld_res,
-                float* out_f32, long long ld_o32, void* out_op, long long ld_oop, int geglu, void* stream) {
+static int gemm_impl(int op_dtype, const void* A, long long lda, const void* W, int M, int N, int K, const float* bias,
+                     const float* row_bias, int rb_div, int ld_rb, const float* residual, long long ld_res,
+                     float* out_f32, long long ld_o32, void* out_op, long long ld_oop, int geglu, float* col_stats,
+                     int stats_hw, void* stream) {
   B200AD_REQUIRE(A && W, "gemm: null operand");
   B200AD_REQUIRE(out_f32 || out_op, "gemm: no output buffer");
   GemmArgs a;
   memset(&a, 0, sizeof(a));
   a.A = A; a.lda = lda; a.W = W; a.M = M; a.N = N; a.K = K;
   fill_epilogue(a.epi, bias, row_bias, rb_div, ld_rb, residual, ld_res, out_f32, ld_o32, out_op, ld_oop, geglu);
+  a.epi.col_stats = col_stats;
+  a.epi.stats_hw = stats_hw;
+  B200AD_REQUIRE(!col_stats || op_dtype == 0, "gemm: column statistics exist on the tcgen05 path only");
   if (op_dtype == 0) return gemm_bf16_tc(a, (cudaStream_t)stream);
   if (op_dtype == 1) return gemm_f32_simt(a, (cudaStream_t)stream);
   set_error("gemm: unknown op_dtype %d", op_dtype);
   return -1;
 }
 
-int b200ad_conv3x3(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout, int mode,
-                   const float* bias, const float* row_bias, int rb_div, int ld_rb, const float* residual,
-                   long long ld_res, float* out_f32, long long ld_o32, void* out_op, long long ld_oop,
-                   void* stream) {
+int b200ad_gemm(int op_dtype, const void* A, long long lda, const void* W, int M, int N, int K, const float* bias,
+                const float* row_bias, int rb_div, int ld_rb, const float* residual, long long ld_res,
+                float* out_f32, long long ld_o32, void* out_op, long long ld_oop, int geglu, void* stream) {
+  return gemm_impl(op_dtype, A, lda, W, M, N, K, bias, row_bias, rb_div, ld_rb, residual, ld_res, out_f32, ld_o32,
+                   out_op, ld_oop, geglu, nullptr, 0, stream);
+}
+
+int b200ad_gemm_stats(int op_dtype, const void* A, long long lda, const void* W, int M, int N, int K,
+                      const float* bias, const float* row_bias, int rb_div, int ld_rb, const float* residual,
+                      long long ld_res, float* out_f32, long long ld_o32, float* col_stats, int rows_per_image,
+                      void* stream) {
+  B200AD_REQUIRE(col_stats, "gemm_stats: null statistics buffer");
+  return gemm_impl(op_dtype, A, lda, W, M, N, K, bias, row_bias, rb_div, ld_rb, residual, ld_res, out_f32, ld_o32,
+                   nullptr, 0, 0, col_stats, rows_per_image, stream);
+}
+
+// M tile of a conv = 128 output pixels = n_box * h_box * w_box (powers of two), chosen to waste the fewest rows
+static void conv_box(int h, int w, int* nb, int* hb, int* wb) {
+  auto best_box = [](int extent, int limit) {
+    int best = 1;
+    double best_eff = -1.0;
+    for (int b = limit; b >= 1; b >>= 1) {
+      const double eff = (double)extent / (double)(((extent + b - 1) / b) * b);
+      if (eff > best_eff + 1e-9) { best_eff = eff; best = b; }
+    }
+    return best;
+  };
+  *wb = best_box(w, 128);
+  *hb = best_box(h, 128 / *wb);
+  *nb = 128 / (*wb * *hb);
+}
+
+int b200ad_stats_slots(int conv, int h, int w) {
+  if (!conv) return (h * w) % 32 == 0 ? (h * w) / 32 : -1;
+  int nb, hb, wb;
+  conv_box(h, w, &nb, &hb, &wb);
+  if (hb * wb < 32) return -1;
+  return ((w + wb - 1) / wb) * ((h + hb - 1) / hb) * (hb * wb / 32);
+}
+
+static int conv_impl(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout, int mode,
+                     const float* bias, const float* row_bias, int rb_div, int ld_rb, const float* residual,
+                     long long ld_res, float* out_f32, long long ld_o32, void* out_op, long long ld_oop,
+                     float* col_stats, void* stream) {
   B200AD_REQUIRE(src && W, "conv3x3: null operand");
   B200AD_REQUIRE(out_f32 || out_op, "conv3x3: no output buffer");
   B200AD_REQUIRE(mode == 0 || mode == 1, "conv3x3: mode %d", mode);
@@ -111,25 +157,31 @@ int b200ad_conv3x3(int op_dtype, const void* src, const void* W, int nimg, int h
         g.tap_dn[t] = (py * 2 + px) * nimg;
       }
     }
-  // M tile = 128 output pixels = n_box * h_box * w_box (powers of two)
-  auto best_box = [](int extent, int limit) {
-    int best = 1;
-    double best_eff = -1.0;
-    for (int b = limit; b >= 1; b >>= 1) {
-      const double eff = (double)extent / (double)(((extent + b - 1) / b) * b);
-      if (eff > best_eff + 1e-9) { best_eff = eff; best = b; }
-    }
-    return best;
-  };
-  const int wb = best_box(w, 128);
-  const int hb = best_box(h, 128 / wb);
-  const int nb = 128 / (wb * hb);
-  g.w_box = wb; g.h_box = hb; g.n_box = nb;
+  conv_box(h, w, &g.n_box, &g.h_box, &g.w_box);
   fill_epilogue(a.epi, bias, row_bias, rb_div, ld_rb, residual, ld_res, out_f32, ld_o32, out_op, ld_oop, 0);
+  a.epi.col_stats = col_stats;
+  B200AD_REQUIRE(!col_stats || op_dtype == 0, "conv3x3: column statistics exist on the tcgen05 path only");
   if (op_dtype == 0) return gemm_bf16_tc(a, (cudaStream_t)stream);
   if (op_dtype == 1) return gemm_f32_simt(a, (cudaStream_t)stream);
   set_error("conv3x3: unknown op_dtype %d", op_dtype);
   return -1;
+}
+
+int b200ad_conv3x3(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout, int mode,
+                   const float* bias, const float* row_bias, int rb_div, int ld_rb, const float* residual,
+                   long long ld_res, float* out_f32, long long ld_o32, void* out_op, long long ld_oop,
+                   void* stream) {
+  return conv_impl(op_dtype, src, W, nimg, h, w, cin, cout, mode, bias, row_bias, rb_div, ld_rb, residual, ld_res,
+                   out_f32, ld_o32, out_op, ld_oop, nullptr, stream);
+}
+
+int b200ad_conv3x3_stats(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout,
+                         int mode, const float* bias, const float* row_bias, int rb_div, int ld_rb,
+                         const float* residual, long long ld_res, float* out_f32, long long ld_o32, float* col_stats,
+                         void* stream) {
+  B200AD_REQUIRE(col_stats, "conv3x3_stats: null statistics buffer");
+  return conv_impl(op_dtype, src, W, nimg, h, w, cin, cout, mode, bias, row_bias, rb_div, ld_rb, residual, ld_res,
+                   out_f32, ld_o32, nullptr, 0, col_stats, stream);
 }
 
 }  // extern "C"

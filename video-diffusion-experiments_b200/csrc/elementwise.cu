@@ -87,6 +87,59 @@ __global__ void gn_finalize_kernel(const float2* __restrict__ partial, int nblk,
   }
 }
 
+// (mean, rstd) per (statistic, group) from the per-(32-row slot, column) sums the producing GEMM / conv epilogue
+// emitted (gemm_tc.cu STATS): float2 st[(image*spi + k)*c + col].  The input is the channel concatenation of up to two
+// tensors with their own statistics buffers.  One block per (statistic, group); fixed summation order (fp32 per thread,
+// fp64 across threads), so the result is deterministic.
+__global__ void __launch_bounds__(256) gn_finalize_colstats_kernel(const float2* __restrict__ st0, int c0, int spi0,
+                                                                   const float2* __restrict__ st1, int c1, int spi1,
+                                                                   int groups, int frames_per_stat, int hw, float eps,
+                                                                   float2* __restrict__ meanrstd) {
+  pdl_enter();
+  __shared__ double red_s[8], red_q[8];
+  const int stat = blockIdx.y, g = blockIdx.x;
+  const int C = c0 + c1, cpg = C / groups;
+  const int ch0 = g * cpg, ch1 = ch0 + cpg;
+  double s = 0.0, q = 0.0;
+  // the group's channels inside source 0 / source 1
+  for (int src = 0; src < 2; ++src) {
+    const float2* st = src ? st1 : st0;
+    const int cs = src ? c1 : c0, off = src ? c0 : 0, spi = src ? spi1 : spi0;
+    if (!st) continue;
+    const int a = max(ch0, off) - off, b = min(ch1, off + cs) - off;
+    if (b <= a) continue;
+    const int wd = b - a;
+    const long long slots = (long long)frames_per_stat * spi;
+    const float2* base = st + ((long long)stat * slots) * cs + a;
+    const long long total = slots * wd;
+    float fs = 0.f, fq = 0.f;
+    for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+      const long long sl = i / wd;
+      const int ch = (int)(i - sl * wd);
+      const float2 v = __ldg(base + sl * cs + ch);
+      fs += v.x; fq += v.y;
+    }
+    s += fs; q += fq;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { red_s[warp] = s; red_q[warp] = q; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    s = 0.0; q = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { s += red_s[w]; q += red_q[w]; }
+    const double cnt = (double)frames_per_stat * hw * cpg;
+    const double mean = s / cnt;
+    double var = q / cnt - mean * mean;
+    if (var < 0.0) var = 0.0;
+    meanrstd[stat * groups + g] = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)eps)));
+  }
+}
+
 template <typename T>
 __global__ void gn_apply_kernel(const float* __restrict__ x0, int c0, const float* __restrict__ x1, int c1, int hw,
                                 int groups, const float2* __restrict__ meanrstd, int frames_per_stat,
@@ -276,6 +329,71 @@ __global__ void gn_apply_vec_kernel(const float* __restrict__ x0, int c0, const 
   }
 }
 
+// Persistent apply: a block keeps its thread <-> (row lane, 4-channel vector) mapping for the whole launch and walks
+// row blocks of R*GN_PU rows (grid-stride), with the NEXT row block's loads in flight while the current one is
+// normalised and stored -- the short-lived blocks of gn_apply_vec_kernel (32 rows each, ~60 KB of traffic, a couple of
+// microseconds of life) left the memory pipe idle at every block turn-over (49 % DRAM utilisation at 28 % occupancy).
+static constexpr int GN_PU = 4;            // rows per thread and row block
+template <typename T>
+__global__ void __launch_bounds__(640) gn_apply_persist_kernel(const float* __restrict__ x0, int c0,
+                                                               const float* __restrict__ x1, int c1, int hw, int groups,
+                                                               int R, const float2* __restrict__ meanrstd,
+                                                               int frames_per_stat, const float* __restrict__ gamma,
+                                                               const float* __restrict__ beta, int silu,
+                                                               T* __restrict__ out, T* __restrict__ raw, int nrb,
+                                                               long long total) {
+  pdl_enter();
+  const int C = c0 + c1;
+  const int nvec = C >> 2;
+  const int cpg = C / groups;
+  const int v = threadIdx.x % nvec, rl = threadIdx.x / nvec;
+  const int c = v * 4;
+  const float4 g4 = *reinterpret_cast<const float4*>(gamma + c);
+  const float4 b4 = *reinterpret_cast<const float4*>(beta + c);
+  const int gi0 = c / cpg, gi1 = (c + 1) / cpg, gi2 = (c + 2) / cpg, gi3 = (c + 3) / cpg;
+  const float* base = (c < c0) ? x0 + c : x1 + (c - c0);
+  const long long ld = (c < c0) ? c0 : c1;
+  const int rows_per_rb = R * GN_PU;
+  float4 cur[GN_PU], nxt[GN_PU];
+  auto load = [&](long long wb, float4* t) {
+    const int n = (int)(wb / nrb), r0 = (int)(wb % nrb) * rows_per_rb;
+#pragma unroll
+    for (int u = 0; u < GN_PU; ++u) {
+      const int rr = r0 + rl + u * R;
+      t[u] = rr < hw ? __ldg(reinterpret_cast<const float4*>(base + ((long long)n * hw + rr) * ld))
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  long long wb = blockIdx.x;
+  if (wb < total) load(wb, cur);
+  for (; wb < total; wb += gridDim.x) {
+    const long long wn = wb + gridDim.x;
+    if (wn < total) load(wn, nxt);
+    const int n = (int)(wb / nrb), r0 = (int)(wb % nrb) * rows_per_rb;
+    const float2* mr = meanrstd + (n / frames_per_stat) * groups;
+    const float2 m0 = mr[gi0], m1 = mr[gi1], m2 = mr[gi2], m3 = mr[gi3];
+    const float s0 = g4.x * m0.y, s1 = g4.y * m1.y, s2 = g4.z * m2.y, s3 = g4.w * m3.y;
+    const float f0 = b4.x - m0.x * s0, f1 = b4.y - m1.x * s1, f2 = b4.z - m2.x * s2, f3 = b4.w - m3.x * s3;
+#pragma unroll
+    for (int u = 0; u < GN_PU; ++u) {
+      const int rr = r0 + rl + u * R;
+      if (rr < hw) {
+        const long long o = ((long long)n * hw + rr) * C + c;
+        float4 y = make_float4(fmaf(cur[u].x, s0, f0), fmaf(cur[u].y, s1, f1), fmaf(cur[u].z, s2, f2),
+                               fmaf(cur[u].w, s3, f3));
+        if (silu) {
+          y.x = __fdividef(y.x, 1.0f + __expf(-y.x)); y.y = __fdividef(y.y, 1.0f + __expf(-y.y));
+          y.z = __fdividef(y.z, 1.0f + __expf(-y.z)); y.w = __fdividef(y.w, 1.0f + __expf(-y.w));
+        }
+        store4<T>(out + o, y);
+        if (raw) store4<T>(raw + o, cur[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < GN_PU; ++u) cur[u] = nxt[u];
+  }
+}
+
 // rows of a block processed side by side by the vectorised kernels (block = R * C/4 threads, ~256..640)
 static int gn_vec_R(int C) {
   const int nvec = C / 4;
@@ -319,6 +437,19 @@ static unsigned int* gn_counters(cudaStream_t st) {
   return buf[dev];
 }
 
+// diagnostics: number of non-zero ticket counters on the current device (0 whenever no GroupNorm is in flight);
+// synchronises the device.  -1: counters not created yet.
+extern "C" int b200ad_gn_counters_nonzero(void) {
+  unsigned int* c = gn_counters(nullptr);
+  if (!c) return -1;
+  static unsigned int host[GN_MAX_COUNTERS];
+  if (cudaDeviceSynchronize() != cudaSuccess) return -2;
+  if (cudaMemcpy(host, c, sizeof(host), cudaMemcpyDeviceToHost) != cudaSuccess) return -2;
+  int nz = 0;
+  for (int i = 0; i < GN_MAX_COUNTERS; ++i) nz += host[i] != 0;
+  return nz;
+}
+
 static int gn_stats_launch(const float* x0, int c0, const float* x1, int c1, int nimg, int hw, int groups,
                            float* partial, void* stream, unsigned int* counters, float2* meanrstd, float eps);
 
@@ -338,6 +469,11 @@ static int gn_stats_launch(const float* x0, int c0, const float* x1, int c1, int
   if (gn_vec_ok(C, c0, groups)) {
     const int R = gn_vec_R(C);
     const dim3 vgrid((gn_nblk(hw) + GN_SB - 1) / GN_SB, nimg);
+    // the ticket counters must be zero when the kernel starts: clear them in stream order (a residue -- e.g. from a
+    // launch on another stream that overlapped this one -- would make an image finalize early on stale partial sums)
+    static const bool ticket_memset = !(getenv("B200AD_GN_TICKET_MEMSET") && atoi(getenv("B200AD_GN_TICKET_MEMSET")) == 0);
+    if (counters && GN_SB == 1 && ticket_memset)
+      B200AD_CHECK_CUDA(cudaMemsetAsync(counters, 0, (size_t)nimg * sizeof(unsigned int), (cudaStream_t)stream));
     if (counters && GN_SB == 1)
       pdl_launch(gn_stats_vec_kernel<true>, dim3(vgrid), dim3(R * (C / 4)), (size_t)R * C * sizeof(float2), (cudaStream_t)stream,
                  x0, c0, x1, c1, hw, groups, R, reinterpret_cast<float2*>(partial), counters, meanrstd, eps);
@@ -354,7 +490,8 @@ static int gn_stats_launch(const float* x0, int c0, const float* x1, int c1, int
 
 static int gn_apply_launch(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
                            int groups, const float* partial, int frames_per_stat, float eps, const float* gamma,
-                           const float* beta, int silu, void* out_op, void* raw_op, void* stream, bool finalize);
+                           const float* beta, int silu, void* out_op, void* raw_op, void* stream, bool finalize,
+                           const float2* meanrstd_in = nullptr);
 
 extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
                                int groups, const float* partial, int frames_per_stat, float eps, const float* gamma,
@@ -365,7 +502,8 @@ extern "C" int b200ad_gn_apply(int op_dtype, const float* x0, int c0, const floa
 
 static int gn_apply_launch(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
                            int groups, const float* partial, int frames_per_stat, float eps, const float* gamma,
-                           const float* beta, int silu, void* out_op, void* raw_op, void* stream, bool finalize) {
+                           const float* beta, int silu, void* out_op, void* raw_op, void* stream, bool finalize,
+                           const float2* meanrstd_in) {
   if (!x1) c1 = 0;
   const int C = c0 + c1;
   B200AD_REQUIRE(groups <= 64 && C % groups == 0 && (C / groups) % 2 == 0 && c0 % 2 == 0,
@@ -377,7 +515,7 @@ static int gn_apply_launch(int op_dtype, const float* x0, int c0, const float* x
   const int nstat = nimg / frames_per_stat;
   // mean / rstd live in the tail of the caller's `partial` buffer (see b200ad.h)
   float2* part = reinterpret_cast<float2*>(const_cast<float*>(partial));
-  float2* meanrstd = part + (long long)nimg * nblk * groups;
+  float2* meanrstd = meanrstd_in ? const_cast<float2*>(meanrstd_in) : part + (long long)nimg * nblk * groups;
   if (finalize) {
     const int warps = nstat * groups;
     const int threads = 256;
@@ -385,7 +523,32 @@ static int gn_apply_launch(int op_dtype, const float* x0, int c0, const float* x
         part, nblk, frames_per_stat, groups, hw, C / groups, eps, meanrstd, nstat);
     count_launch();
   }
-  if (gn_vec_ok(C, c0, groups)) {
+  static const bool persist = !(getenv("B200AD_GN_PERSIST") && atoi(getenv("B200AD_GN_PERSIST")) == 0);
+  if (gn_vec_ok(C, c0, groups) && persist) {
+    const int R = gn_vec_R(C);
+    const int threads = R * (C / 4);
+    const int nrb = (hw + R * GN_PU - 1) / (R * GN_PU);
+    const long long total = (long long)nimg * nrb;
+    static int sms = 0;
+    if (!sms) {
+      int dev = 0;
+      B200AD_CHECK_CUDA(cudaGetDevice(&dev));
+      B200AD_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    }
+    int per_sm = 2048 / threads;                    // resident blocks (<= 64 registers per thread)
+    if (per_sm > 6) per_sm = 6;
+    if (per_sm < 1) per_sm = 1;
+    const long long want = (long long)sms * per_sm;
+    const int blocks = (int)(total < want ? total : want);
+    if (op_dtype == 0)
+      pdl_launch(gn_apply_persist_kernel<bf16>, dim3(blocks), dim3(threads), (size_t)0, (cudaStream_t)stream, x0, c0, x1, c1,
+                 hw, groups, R, (const float2*)meanrstd, frames_per_stat, gamma, beta, silu, (bf16*)out_op, (bf16*)raw_op,
+                 nrb, total);
+    else
+      pdl_launch(gn_apply_persist_kernel<float>, dim3(blocks), dim3(threads), (size_t)0, (cudaStream_t)stream, x0, c0, x1,
+                 c1, hw, groups, R, (const float2*)meanrstd, frames_per_stat, gamma, beta, silu, (float*)out_op,
+                 (float*)raw_op, nrb, total);
+  } else if (gn_vec_ok(C, c0, groups)) {
     const int R = gn_vec_R(C);
     const dim3 vgrid((gn_nblk(hw) + GN_SB - 1) / GN_SB, nimg);
     if (op_dtype == 0)
@@ -403,6 +566,27 @@ static int gn_apply_launch(int op_dtype, const float* x0, int c0, const float* x
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+// GroupNorm whose statistics come from the producer's epilogue: finalize (tiny) + apply; the fp32 input is read ONCE.
+extern "C" int b200ad_gn_apply_stats(int op_dtype, const float* x0, int c0, const float* st0, int spi0,
+                                     const float* x1, int c1, const float* st1, int spi1, int nimg, int hw, int groups,
+                                     int frames_per_stat, float eps, const float* gamma, const float* beta, int silu,
+                                     float* meanrstd_ws, void* out_op, void* raw_op, void* stream) {
+  if (!x1) { c1 = 0; st1 = nullptr; }
+  const int C = c0 + c1;
+  B200AD_REQUIRE(st0 && (c1 == 0 || st1) && meanrstd_ws, "gn_apply_stats: null statistics / workspace");
+  B200AD_REQUIRE(groups <= 64 && C % groups == 0, "gn_apply_stats: C=%d groups=%d", C, groups);
+  B200AD_REQUIRE(frames_per_stat >= 1 && nimg % frames_per_stat == 0, "gn_apply_stats: nimg=%d frames_per_stat=%d", nimg,
+                 frames_per_stat);
+  const int nstat = nimg / frames_per_stat;
+  pdl_launch(gn_finalize_colstats_kernel, dim3(groups, nstat), dim3(256), (size_t)0, (cudaStream_t)stream,
+             reinterpret_cast<const float2*>(st0), c0, spi0, reinterpret_cast<const float2*>(st1), c1, spi1, groups,
+             frames_per_stat, hw, eps, reinterpret_cast<float2*>(meanrstd_ws));
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return gn_apply_launch(op_dtype, x0, c0, x1, c1, nimg, hw, groups, nullptr, frames_per_stat, eps, gamma, beta, silu,
+                         out_op, raw_op, stream, false, reinterpret_cast<const float2*>(meanrstd_ws));
 }
 
 // Fused GroupNorm: statistics + finalize + apply in one call (same workspace layout as gn_stats/gn_apply).  Optionally

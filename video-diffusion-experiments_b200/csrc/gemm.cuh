@@ -29,6 +29,11 @@ struct Epilogue {
   void* out_op;                // operand-typed output (bf16 on the tcgen05 path, fp32 on the SIMT path) or null
   long long ld_oop;
   int geglu;                   // 1: columns are interleaved (h0,g0,h1,g1,...); writes N/2 columns h*gelu(g)
+  // GroupNorm statistics of the fp32 OUTPUT, emitted by the epilogue (tcgen05 path only): per 32-row slot and column
+  // (sum, sum of squares) as float2 col_stats[(image * stats_spi + k) * N + col]; the GroupNorm that consumes out_f32
+  // then needs no statistics pass over the tensor (b200ad_gn_apply_stats).  Dense rows: image = row / stats_hw.
+  float* col_stats;
+  int stats_hw;                // rows per image (dense GEMM; conv uses its own geometry)
 };
 
 struct GemmArgs {

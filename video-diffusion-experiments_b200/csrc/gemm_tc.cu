@@ -61,6 +61,10 @@ struct TcParams {
   const float* row_bias;
   int rb_div, ld_rb;
   long long* dbg;              // optional [grid][16] cycle counters (b200ad_debug_buffer), null in production
+  // GroupNorm column statistics of the fp32 output (STATS instantiations): float2 [(image*spi + k)*N + col]
+  float2* stats;
+  int stats_spi;               // 32-row slots per image
+  int stats_qpi;               // conv: slots per image inside one tile (h_box*w_box/32); dense: unused
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -256,7 +260,16 @@ __device__ __forceinline__ void io_group_init(const TcParams& p, const EpiMaps& 
 // EPI: the epilogue's output combination as a compile-time constant -- a bit mask (8 GEGLU, 4 residual, 2 fp32 output,
 // 1 operand output) for the combinations the UNet uses, or -1 for run-time flags.  With run-time flags every chunk of
 // the epilogue loops went through five uniform branches, and a branch is a scheduling barrier (as in attn_fa.cu).
-template <int EPI>
+__device__ __forceinline__ float lds_f1(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+
+// STATS: the math warps also emit per-(32-row slot, column) sum / sum of squares of the fp32 output they just wrote
+// to the chunk buffer (each warp owns rows quarter*32 .. +31 of the tile: lane l re-reads column l of those rows from
+// the swizzled buffer, conflict-free), so the GroupNorm that follows needs no statistics pass over the tensor.
+template <int EPI, bool STATS = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ EpiMaps em, const __grid_constant__ TcParams p) {
@@ -529,6 +542,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (out_row > p.M - 1) out_row = p.M - 1;
         }
       }
+      // column statistics: which rows of this warp's quarter exist, and the slot they are summed into
+      uint32_t st_mask = 0;
+      float2* st_row = nullptr;
+      if (STATS) {
+        bool valid;
+        long long slot;
+        bool slot_ok;
+        if (p.conv) {
+          const int x = t.x0 + (r % p.w_box), y = t.y0 + ((r / p.w_box) % p.h_box);
+          const int n = t.n0 + r / (p.w_box * p.h_box);
+          valid = x < p.w && y < p.h && n < p.nimg;
+          const int img = t.n0 + quarter / p.stats_qpi;
+          slot_ok = img < p.nimg;
+          slot = (long long)img * p.stats_spi + (t.m_tile % (p.tiles_x * p.tiles_y)) * p.stats_qpi + quarter % p.stats_qpi;
+        } else {
+          valid = (long long)t.m_tile * BM + r < p.M;
+          slot = (long long)t.m_tile * 4 + quarter;
+          slot_ok = (long long)t.m_tile * BM + quarter * 32 < p.M;
+        }
+        st_mask = __ballot_sync(0xffffffffu, valid);
+        if (slot_ok) st_row = p.stats + slot * p.N + t.n_tile * p.BN + lane;
+      }
       const long long q0 = prof_clock();
       const float* bias_t = p.bias ? p.bias + t.n_tile * p.BN : nullptr;
       const float* rb_row =
@@ -606,6 +641,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             sts_u4(rowa + (uint32_t)((j ^ sw) << 4), pack_bf16x2(v[8 * j], v[8 * j + 1]),
                    pack_bf16x2(v[8 * j + 2], v[8 * j + 3]), pack_bf16x2(v[8 * j + 4], v[8 * j + 5]),
                    pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+        }
+        if (STATS) {
+          __syncwarp();                       // this warp's 32 rows of the chunk are in the buffer
+          const uint32_t colw = (uint32_t)((lane & 3) << 2);
+          const uint32_t base = smem_u32(fb) + (uint32_t)(quarter * 32 * 128);
+          float s0 = 0.f, s1 = 0.f, q0_ = 0.f, q1_ = 0.f;
+#pragma unroll
+          for (int rr = 0; rr < 32; rr += 2) {
+            float x0 = lds_f1(base + (uint32_t)(rr * 128) + (uint32_t)((((lane >> 2) ^ (rr & 7)) << 4)) + colw);
+            float x1 = lds_f1(base + (uint32_t)((rr + 1) * 128) + (uint32_t)((((lane >> 2) ^ ((rr + 1) & 7)) << 4)) + colw);
+            if (!((st_mask >> rr) & 1u)) x0 = 0.f;
+            if (!((st_mask >> (rr + 1)) & 1u)) x1 = 0.f;
+            s0 += x0; q0_ = fmaf(x0, x0, q0_);
+            s1 += x1; q1_ = fmaf(x1, x1, q1_);
+          }
+          if (st_row) st_row[c * 32] = make_float2(s0 + s1, q0_ + q1_);
         }
         fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store
         mbar_arrive(&cdone[buf]);
@@ -689,6 +740,7 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   p.has_oop = e.out_op != nullptr;
   p.geglu = e.geglu;
   p.dbg = g_dbg;
+  p.stats = reinterpret_cast<float2*>(e.col_stats);
   p.bias = e.bias; p.row_bias = e.row_bias; p.rb_div = e.rb_div > 0 ? e.rb_div : 1; p.ld_rb = e.ld_rb;
   if (e.geglu) {
     B200AD_REQUIRE(e.out_op && !e.out_f32 && !e.residual && !e.row_bias, "geglu epilogue writes out_op only");
@@ -726,6 +778,19 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     uint64_t strides[1] = {(uint64_t)a.lda * 2};
     uint32_t box[2] = {(uint32_t)BK, (uint32_t)BM};
     if (int rc = make_tmap_bf16(&tmA, a.A, 2, dims, strides, box)) return rc;
+  }
+  if (p.stats) {
+    B200AD_REQUIRE(e.out_f32 && !e.geglu, "gemm: column statistics need an fp32 output");
+    if (g.enabled) {
+      p.stats_qpi = g.h_box * g.w_box / 32;
+      B200AD_REQUIRE(p.stats_qpi >= 1, "conv: column statistics need >= 32 pixels of one image per tile (box %dx%dx%d)",
+                     g.n_box, g.h_box, g.w_box);
+      p.stats_spi = p.tiles_x * p.tiles_y * p.stats_qpi;
+    } else {
+      B200AD_REQUIRE(e.stats_hw > 0 && e.stats_hw % 32 == 0 && a.M % e.stats_hw == 0,
+                     "gemm: column statistics need rows per image (%d) to be a multiple of 32 dividing M=%d", e.stats_hw, a.M);
+      p.stats_spi = e.stats_hw / 32;
+    }
   }
   p.num_m_pairs = (num_m_tiles + 1) / 2;
   const int max_clusters = g_num_sms / 2;
@@ -792,6 +857,8 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
     B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+    B200AD_CHECK_CUDA((cudaFuncSetAttribute(gemm_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)));
+    B200AD_CHECK_CUDA((cudaFuncSetAttribute(gemm_tc_kernel<6, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)));
     g_attr_set = true;
   }
   const long long tiles = (long long)p.num_m_pairs * p.num_n_tiles;
@@ -811,6 +878,13 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  if (p.stats) {
+    B200AD_REQUIRE(epi_mask == 2 || epi_mask == 6, "gemm: column statistics are implemented for fp32-only outputs (mask %d)", epi_mask);
+    if (epi_mask == 2) B200AD_CHECK_CUDA((cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2, true>, tmA, tmB, em, p)));
+    else B200AD_CHECK_CUDA((cudaLaunchKernelEx(&cfg, gemm_tc_kernel<6, true>, tmA, tmB, em, p)));
+    count_launch();
+    return 0;
+  }
   switch (epi_known ? epi_mask : -1) {
     case 1: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<1>, tmA, tmB, em, p)); break;
     case 2: B200AD_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2>, tmA, tmB, em, p)); break;

@@ -93,10 +93,25 @@ class Conv2d(nn.Conv2d, _LeafCache):
         k, s, pad = self.kernel_size[0], self.stride[0], self.padding[0]
         bias = lambda: None if self.bias is None else self.bias.detach().float().contiguous()
         if k == 1 and s == 1 and pad == 0:
-            p = self._packed(o, lambda: {"w": self.weight.detach().reshape(cout, cin).to(o.op_dtype).contiguous(),
-                                         "b": bias()})
+            # the tensor-core GEMM wants N % 32 == 0 and K % 8 == 0: tiny 1x1 convs (the VAE's post_quant_conv, 4 -> 4)
+            # are zero-padded to that shape
+            kp, np_ = (cin + 7) // 8 * 8, (cout + 31) // 32 * 32
+
+            def build():
+                wp = torch.zeros(np_, kp, device=self.weight.device, dtype=torch.float32)
+                wp[:cout, :cin] = self.weight.detach().reshape(cout, cin).float()
+                bp = None
+                if self.bias is not None:
+                    bp = torch.zeros(np_, device=self.weight.device, dtype=torch.float32)
+                    bp[:cout] = self.bias.detach().float()
+                return {"w": wp.to(o.op_dtype).contiguous(), "b": bp}
+            p = self._packed(o, build)
             r = nchw_to_rows(x)
-            y, _ = o.gemm(o.cast(r, 1, 1, r.shape[0], cin), p["w"], bias=p["b"], want_f32=True)
+            if kp != cin:
+                r = torch.nn.functional.pad(r, (0, kp - cin))
+            y, _ = o.gemm(o.cast(r, 1, 1, r.shape[0], kp), p["w"], bias=p["b"], want_f32=True)
+            if np_ != cout:
+                y = y[:, :cout].contiguous()
             return rows_to_nchw(y, n, h, w, x.dtype)
         if not (k == 3 and pad == 1 and s in (1, 2)):
             raise NotImplementedError(f"b200ad Conv2d: kernel {k} stride {s} padding {pad} is not on the AnimateDiff path")

@@ -5,6 +5,8 @@ All functions require CUDA tensors and raise otherwise -- there is no CPU fallba
 """
 from __future__ import annotations
 
+import os
+import weakref
 from typing import Optional
 
 import torch
@@ -81,18 +83,36 @@ class Ops:
     def _rec(self, name, flops=0.0, nbytes=0.0):
         return _Rec(Ops.profiler, name, flops, nbytes)
 
+    # GroupNorm column statistics emitted by GEMM / conv epilogues: data_ptr of the fp32 output -> (stats, spi, nimg,
+    # hw, C, out tensor).  A later writer of the same buffer without statistics drops the entry.
+    use_epilogue_stats = os.environ.get("B200AD_EPILOGUE_STATS", "1") != "0"      # A/B switch for measurements
+
     def __init__(self, mode: str = "bf16"):
         if mode not in ("bf16", "fp32"):
             raise ValueError(f"mode must be 'bf16' or 'fp32', got {mode!r}")
+        self.colstats = {}
         self.mode = mode
         self.op = BF16 if mode == "bf16" else FP32
         self.op_dtype = torch.bfloat16 if mode == "bf16" else torch.float32
         self.L = _lib.load()
 
     # ---------------------------------------------------------------- contractions
+    def _stats_ok(self, conv: bool, h: int, w: int) -> int:
+        """32-row statistic slots per image the epilogue can emit for this geometry, or 0 (fp32 mode / unsupported)."""
+        if self.op != BF16 or not Ops.use_epilogue_stats:
+            return 0
+        spi = self.L.b200ad_stats_slots(1 if conv else 0, h, w)
+        return spi if spi > 0 else 0
+
+    def _forget_stats(self, out_f32):
+        if out_f32 is not None and self.colstats:
+            self.colstats.pop(out_f32.data_ptr(), None)
+
     def gemm(self, a, w, *, bias=None, row_bias=None, rb_div=1, residual=None, out_f32=None, out_op=None,
-             want_f32=False, want_op=False, geglu=False):
-        """C = a[M,K] @ w[N,K]^T with fused epilogue (b200ad_gemm).  Returns (out_f32, out_op)."""
+             want_f32=False, want_op=False, geglu=False, stats_hw=None):
+        """C = a[M,K] @ w[N,K]^T with fused epilogue (b200ad_gemm).  Returns (out_f32, out_op).
+        stats_hw (rows per image): the fp32 output feeds a GroupNorm -- its per-column sums are emitted by the epilogue
+        (b200ad_gemm_stats) and remembered for group_norm()."""
         _need_cuda(a, w)
         assert a.dim() == 2 and w.dim() == 2 and a.dtype == self.op_dtype and w.dtype == self.op_dtype
         assert a.stride(1) == 1 and w.is_contiguous()
@@ -104,6 +124,21 @@ class Ops:
             out_f32 = torch.empty((M, n_out), device=a.device, dtype=torch.float32)
         if want_op and out_op is None:
             out_op = torch.empty((M, n_out), device=a.device, dtype=self.op_dtype)
+        spi = self._stats_ok(False, stats_hw, 1) if (stats_hw and out_f32 is not None and out_op is None and not geglu
+                                                     and M % stats_hw == 0) else 0
+        if spi:
+            nimg = M // stats_hw
+            st = torch.empty((nimg * spi, N, 2), device=a.device, dtype=torch.float32)
+            with self._rec("gemm", 2.0 * M * N * K, _nb(w, residual, out_f32, st) + M * K * a.element_size()):
+                rc = self.L.b200ad_gemm_stats(
+                    self.op, a.data_ptr(), a.stride(0), w.data_ptr(), M, N, K, _ptr(bias), _ptr(row_bias), rb_div,
+                    0 if row_bias is None else row_bias.stride(0), _ptr(residual),
+                    0 if residual is None else residual.stride(0), out_f32.data_ptr(), out_f32.stride(0),
+                    st.data_ptr(), stats_hw, _stream())
+            _lib.check(rc, "b200ad_gemm_stats")
+            self.colstats[out_f32.data_ptr()] = (st, spi, nimg, stats_hw, N, weakref.ref(out_f32))
+            return out_f32, None
+        self._forget_stats(out_f32)
         with self._rec("gemm", 2.0 * M * N * K, _nb(w, residual, out_f32, out_op) + M * K * a.element_size()):
             rc = self.L.b200ad_gemm(
                 self.op, a.data_ptr(), a.stride(0), w.data_ptr(), M, N, K, _ptr(bias), _ptr(row_bias), rb_div,
@@ -115,8 +150,9 @@ class Ops:
         return out_f32, out_op
 
     def conv3x3(self, src, w, nimg, h, wd, *, stride2=False, bias=None, row_bias=None, rb_div=1, residual=None,
-                want_f32=True, want_op=False):
-        """3x3 conv over NHWC `src` (operand-typed); w [cout, 9*cin].  Returns (out_f32 [nimg*h*wd, cout], out_op)."""
+                want_f32=True, want_op=False, stats=False):
+        """3x3 conv over NHWC `src` (operand-typed); w [cout, 9*cin].  Returns (out_f32 [nimg*h*wd, cout], out_op).
+        stats: the fp32 output feeds a GroupNorm (see gemm)."""
         _need_cuda(src, w)
         assert src.dtype == self.op_dtype and w.dtype == self.op_dtype and src.is_contiguous() and w.is_contiguous()
         cout, k9 = w.shape
@@ -124,6 +160,17 @@ class Ops:
         M = nimg * h * wd
         out_f32 = torch.empty((M, cout), device=src.device, dtype=torch.float32) if want_f32 else None
         out_op = torch.empty((M, cout), device=src.device, dtype=self.op_dtype) if want_op else None
+        spi = self._stats_ok(True, h, wd) if (stats and want_f32 and not want_op) else 0
+        if spi:
+            st = torch.empty((nimg * spi, cout, 2), device=src.device, dtype=torch.float32)
+            with self._rec("conv3x3", 2.0 * M * cout * k9, _nb(src, w, residual, out_f32, st)):
+                rc = self.L.b200ad_conv3x3_stats(
+                    self.op, src.data_ptr(), w.data_ptr(), nimg, h, wd, cin, cout, 1 if stride2 else 0, _ptr(bias),
+                    _ptr(row_bias), rb_div, 0 if row_bias is None else row_bias.stride(0), _ptr(residual),
+                    0 if residual is None else residual.stride(0), out_f32.data_ptr(), cout, st.data_ptr(), _stream())
+            _lib.check(rc, "b200ad_conv3x3_stats")
+            self.colstats[out_f32.data_ptr()] = (st, spi, nimg, h * wd, cout, weakref.ref(out_f32))
+            return out_f32, None
         with self._rec("conv3x3", 2.0 * M * cout * k9, _nb(src, w, residual, out_f32, out_op)):
             rc = self.L.b200ad_conv3x3(
                 self.op, src.data_ptr(), w.data_ptr(), nimg, h, wd, cin, cout, 1 if stride2 else 0, _ptr(bias),
@@ -165,17 +212,38 @@ class Ops:
         c1 = 0 if x1 is None else x1.shape[-1]
         if x1 is not None:
             assert x1.dtype == torch.float32 and x1.is_contiguous()
-        nblk = self.L.b200ad_gn_nblk(hw)
-        partial = torch.empty((nimg * nblk * groups + nimg * groups, 2), device=x0.device, dtype=torch.float32)
         out = torch.empty((nimg * hw, c0 + c1), device=x0.device, dtype=self.op_dtype)
         raw = torch.empty_like(out) if want_raw else None
-        # algorithmic bytes: the input twice (statistics, apply) + the operand-typed output(s)
-        with self._rec("group_norm", 0.0, 2 * _nb(x0, x1) + _nb(out, raw)):
+        # statistics from the producers' epilogues (every source must have them, for this geometry)
+        s0 = self._lookup_stats(x0, nimg, hw, c0)
+        s1 = self._lookup_stats(x1, nimg, hw, c1) if x1 is not None else None
+        if s0 is not None and (x1 is None or s1 is not None) and (c0 + c1) // groups % 2 == 0 and c0 % 2 == 0:
+            ws = torch.empty((nimg // frames_per_stat * groups, 2), device=x0.device, dtype=torch.float32)
+            # algorithmic bytes: the fp32 input ONCE + the operand-typed output(s)
+            with self._rec("group_norm", 0.0, _nb(x0, x1) + _nb(out, raw)):
+                rc = self.L.b200ad_gn_apply_stats(
+                    self.op, x0.data_ptr(), c0, s0[0].data_ptr(), s0[1], _ptr(x1), c1,
+                    None if s1 is None else s1[0].data_ptr(), 0 if s1 is None else s1[1], nimg, hw, groups,
+                    frames_per_stat, float(eps), gamma.data_ptr(), beta.data_ptr(), 1 if silu else 0, ws.data_ptr(),
+                    out.data_ptr(), _ptr(raw), _stream())
+            _lib.check(rc, "b200ad_gn_apply_stats")
+            return (out, raw) if want_raw else out
+        nblk = self.L.b200ad_gn_nblk(hw)
+        partial = torch.empty((nimg * nblk * groups + nimg * groups, 2), device=x0.device, dtype=torch.float32)
+        # algorithmic bytes (1 read + 1 write is the floor): the fp32 input once + the operand-typed output(s); this
+        # path READS the input twice (statistics pass, apply pass)
+        with self._rec("group_norm", 0.0, _nb(x0, x1) + _nb(out, raw)):
             rc = self.L.b200ad_group_norm(self.op, x0.data_ptr(), c0, _ptr(x1), c1, nimg, hw, groups,
                                           partial.data_ptr(), frames_per_stat, float(eps), gamma.data_ptr(),
                                           beta.data_ptr(), 1 if silu else 0, out.data_ptr(), _ptr(raw), _stream())
         _lib.check(rc, "b200ad_group_norm")
         return (out, raw) if want_raw else out
+
+    def _lookup_stats(self, x, nimg, hw, c):
+        e = self.colstats.get(x.data_ptr()) if self.colstats else None
+        if e is None or e[5]() is not x or e[2:5] != (nimg, hw, c):
+            return None
+        return e
 
     def layer_norm(self, x, gamma, beta, eps=1e-5, pe=None, hw=1, frames=1):
         _need_cuda(x)

@@ -104,7 +104,8 @@ def is_done(run: ExperimentConfig, output_dir: Path) -> bool:
 
 
 def save_experiment(frames, run: ExperimentConfig, output_dir: Path) -> Path:
-    """frames/frame_%04d.png, <id>.gif, then config.json LAST (it is the completion marker) -- 05:172-190."""
+    """frames/frame_%04d.png, <id>.gif, then config.json LAST (it is the completion marker) -- 05:172-190.
+    `frames`: list of PIL images (the reference's synchronous form; the sweep itself uses FrameExporter)."""
     exp_dir = Path(output_dir) / run.experiment_id
     frames_dir = exp_dir / "frames"
     frames_dir.mkdir(parents=True, exist_ok=True)
@@ -113,11 +114,109 @@ def save_experiment(frames, run: ExperimentConfig, output_dir: Path) -> Path:
             fr.save(frames_dir / f"frame_{i:04d}.png")
         frames[0].save(os.fspath(exp_dir / f"{run.experiment_id}.gif"), save_all=True, append_images=frames[1:],
                        optimize=False, duration=100, loop=0)
+    _write_marker(run, exp_dir)
+    return exp_dir
+
+
+class FrameExporter:
+    """Frame export overlapped with the next video.  The reference saves 16 PNGs and a GIF
+    synchronously between videos (05:172-190); at ~1 s of GPU time per video that stall would be a large share of the
+    sweep.  Here the writer rank hands the uint8 frames (device tensor [F,H,W,3]) over: they are copied to pinned host
+    memory on a side stream, PNG / GIF encoding runs on a small thread pool (PIL releases the GIL while it compresses),
+    and config.json -- the completion marker -- is written only after every file of the run is on disk."""
+
+    def __init__(self, output_dir: Path, threads: int = 4, synchronous: bool = False):
+        import concurrent.futures as cf
+        import threading
+        self.out = Path(output_dir)
+        self.sync = synchronous
+        # >= 3 threads: up to two per-run tasks wait on their frame tasks, which need a free thread of the same pool
+        self.pool = None if synchronous else cf.ThreadPoolExecutor(max_workers=max(3, threads), thread_name_prefix="export")
+        self.pending = []
+        self.lock = threading.Lock()
+        self.encode_seconds = 0.0        # summed over threads
+        self.stall_seconds = 0.0         # time the generating thread spent waiting for the exporter
+        self.copy_stream = None
+
+    def _timed(self, fn, *a):
+        t0 = time.perf_counter()
+        fn(*a)
+        with self.lock:
+            self.encode_seconds += time.perf_counter() - t0
+
+    def submit(self, frames_u8, run: "ExperimentConfig"):
+        """frames_u8: uint8 [F,H,W,3] CUDA tensor (or None for marker-only runs)."""
+        import torch
+        exp_dir = self.out / run.experiment_id
+        (exp_dir / "frames").mkdir(parents=True, exist_ok=True)
+        if frames_u8 is None:
+            _write_marker(run, exp_dir)
+            return
+        t0 = time.perf_counter()
+        if self.sync:
+            arr = frames_u8.cpu().numpy()
+            self._timed(_encode_run, arr, run, exp_dir)
+            self.stall_seconds += time.perf_counter() - t0
+            return
+        if self.copy_stream is None:
+            self.copy_stream = torch.cuda.Stream()
+        host = torch.empty(frames_u8.shape, dtype=torch.uint8, pin_memory=True)
+        self.copy_stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.copy_stream):
+            host.copy_(frames_u8, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+        frames_u8.record_stream(self.copy_stream)
+        # bound the backlog: at most two videos in flight behind the generator
+        while len(self.pending) >= 2:
+            self.pending.pop(0).result()
+        self.pending.append(self.pool.submit(self._export_async, host, ev, run, exp_dir))
+        self.stall_seconds += time.perf_counter() - t0
+
+    def _export_async(self, host, ev, run, exp_dir):
+        ev.synchronize()
+        arr = host.numpy()
+        # frames in parallel on the pool's other threads, GIF here; the marker after all of them
+        futs = [self.pool.submit(self._timed, _encode_png, arr[i], exp_dir / "frames" / f"frame_{i:04d}.png")
+                for i in range(arr.shape[0])]
+        self._timed(_encode_gif, arr, exp_dir / f"{run.experiment_id}.gif")
+        for f in futs:
+            f.result()
+        _write_marker(run, exp_dir)
+
+    def finish(self):
+        t0 = time.perf_counter()
+        for f in self.pending:
+            f.result()
+        self.pending.clear()
+        if self.pool is not None:
+            self.pool.shutdown(wait=True)
+        self.stall_seconds += time.perf_counter() - t0
+
+
+def _encode_png(frame, path):
+    from PIL import Image
+    Image.fromarray(frame).save(path)
+
+
+def _encode_gif(arr, path):
+    from PIL import Image
+    frames = [Image.fromarray(f) for f in arr]
+    frames[0].save(os.fspath(path), save_all=True, append_images=frames[1:], optimize=False, duration=100, loop=0)
+
+
+def _encode_run(arr, run, exp_dir):
+    for i in range(arr.shape[0]):
+        _encode_png(arr[i], exp_dir / "frames" / f"frame_{i:04d}.png")
+    _encode_gif(arr, exp_dir / f"{run.experiment_id}.gif")
+    _write_marker(run, exp_dir)
+
+
+def _write_marker(run: "ExperimentConfig", exp_dir: Path):
     tmp = exp_dir / "config.json.tmp"
     with open(tmp, "w") as f:
         json.dump(asdict(run), f, indent=2)
     os.replace(tmp, exp_dir / "config.json")
-    return exp_dir
 
 
 def generate_manifest(output_dir: Path) -> dict:
@@ -146,26 +245,44 @@ def worker_layout(world: int, pair: bool):
 
 
 def run_worker(pipe, my_runs: Sequence[ExperimentConfig], output_dir: Path, writer: bool, decode: bool = True,
-               log=print) -> dict:
-    """Walk one worker's list the way the reference's loops do (generate -> save -> marker).  In a CFG pair
-    both ranks call the pipeline (they stay in lock-step through the per-step all-gather); only `writer` saves."""
+               log=print, sync_export: bool = False, export_threads: int = 4) -> dict:
+    """Walk one worker's list the way the reference's loops do (generate -> save -> marker).  In a CFG pair both
+    ranks run the denoise loop (they stay in lock-step through the per-step all-gather); only `writer` decodes the
+    latents (b200ad VAE -> uint8 frames on the device) and exports, overlapped with the next video (FrameExporter)."""
     import torch
+    exporter = FrameExporter(output_dir, threads=export_threads, synchronous=sync_export) if writer else None
     done_steps, done_runs, t0 = 0, 0, time.perf_counter()
+    t_denoise = t_decode = 0.0
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     for run in my_runs:
         if is_done(run, output_dir):
             log(f"  Skipping {run.experiment_id} (already exists)")
             continue
         generator = torch.Generator().manual_seed(run.seed)          # 05:156 torch.manual_seed(seed): CPU generator
+        ev[0].record()
         out = pipe(prompt=run.prompt, negative_prompt=run.negative_prompt, num_frames=run.num_frames,
                    guidance_scale=run.guidance_scale, num_inference_steps=run.num_inference_steps,
-                   height=run.height, width=run.width, generator=generator,
-                   output_type="pil" if decode else "latent")
+                   height=run.height, width=run.width, generator=generator, output_type="latent")
+        ev[1].record()
+        frames = None
+        if writer and decode:
+            frames = pipe.vae.decode_video_u8(out.frames.float())   # [F, H, W, 3] uint8, still on the device
+        ev[2].record()
         if writer:
-            save_experiment(out.frames[0] if decode else None, run, output_dir)
+            exporter.submit(frames, run)
+        ev[2].synchronize()
+        t_denoise += ev[0].elapsed_time(ev[1]) * 1e-3
+        t_decode += ev[1].elapsed_time(ev[2]) * 1e-3
         done_steps += run.num_inference_steps
         done_runs += 1
     torch.cuda.synchronize()
-    return {"runs": done_runs, "steps": done_steps, "seconds": time.perf_counter() - t0}
+    t_gen = time.perf_counter() - t0
+    if exporter is not None:
+        exporter.finish()
+    return {"runs": done_runs, "steps": done_steps, "seconds": time.perf_counter() - t0, "generate_seconds": t_gen,
+            "denoise_seconds": t_denoise, "decode_seconds": t_decode,
+            "export_encode_seconds": 0.0 if exporter is None else exporter.encode_seconds,
+            "export_stall_seconds": 0.0 if exporter is None else exporter.stall_seconds}
 
 
 def main(argv=None) -> int:
@@ -181,6 +298,9 @@ def main(argv=None) -> int:
     ap.add_argument("--no-pairs", action="store_true", help="one worker per GPU instead of CFG-split pairs")
     ap.add_argument("--latent-only", action="store_true", help="skip VAE decode / frame export (markers only)")
     ap.add_argument("--limit", type=int, default=0, help="only the first LIMIT runs (smoke runs)")
+    ap.add_argument("--sync-export", action="store_true",
+                    help="encode PNG/GIF synchronously between videos, as the reference does (05:172-190)")
+    ap.add_argument("--export-threads", type=int, default=4)
     ap.add_argument("--height", type=int, default=HEIGHT)
     ap.add_argument("--width", type=int, default=WIDTH)
     a = ap.parse_args(argv)
@@ -222,33 +342,44 @@ def main(argv=None) -> int:
     pipe.scheduler = DDIMScheduler.from_config(pipe.scheduler.config, beta_schedule="linear", steps_offset=1,
                                                clip_sample=False)                             # 05:136-141
     pipe.cfg_group = group
-    stats = run_worker(pipe, mine, out_dir, writer=(rank % per == 0), decode=not a.latent_only,
-                       log=lambda m: print(f"[worker {worker}] {m}", flush=True))
-    t = torch.tensor([stats["seconds"], float(stats["steps"]) if rank % per == 0 else 0.0,
-                      float(stats["runs"]) if rank % per == 0 else 0.0], device="cuda", dtype=torch.float64)
+    ok = False
+    try:
+        stats = run_worker(pipe, mine, out_dir, writer=(rank % per == 0), decode=not a.latent_only,
+                           log=lambda m: print(f"[worker {worker}] {m}", flush=True), sync_export=a.sync_export,
+                           export_threads=a.export_threads)
+        is_w = rank % per == 0
+        keys = ("steps", "runs", "denoise_seconds", "decode_seconds", "export_encode_seconds", "export_stall_seconds")
+        t = torch.tensor([stats["seconds"]] + [float(stats[k]) if is_w else 0.0 for k in keys], device="cuda",
+                         dtype=torch.float64)
+        if world > 1:
+            tmax = t.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            t[0] = tmax[0]
+        if rank == 0:
+            generate_manifest(out_dir)
+            secs = float(t[0])
+            tot = dict(zip(keys, [float(v) for v in t[1:]]))
+            print(json.dumps({"sweep_runs": int(tot["runs"]), "denoise_steps": int(tot["steps"]), "seconds": secs,
+                              "steps_per_s": tot["steps"] / secs if secs else None,
+                              "videos_per_hour": tot["runs"] * 3600 / secs if secs else None, "n_gpus": world,
+                              "workers": n_workers, "gpus_per_worker": per,
+                              "layout": "pairs" if per == 2 else "replicas", "decode": not a.latent_only,
+                              "export": "synchronous" if a.sync_export else f"overlapped ({a.export_threads} threads)",
+                              "sum_over_workers": {k: round(v, 3) for k, v in tot.items() if k.endswith("seconds")},
+                              "what": "wall clock of the slowest worker from its first video to its last marker on disk: "
+                                      "denoise loop + VAE decode + uint8 + PNG x16 + GIF + config.json per run"}),
+                  flush=True)
+        ok = True
+    except BaseException:
+        import traceback
+        traceback.print_exc()
+        if world == 1:
+            raise
     if world > 1:
-        tmax = t.clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        t[0] = tmax[0]
-    if rank == 0:
-        generate_manifest(out_dir)
-        secs, steps, nruns = float(t[0]), float(t[1]), float(t[2])
-        print(json.dumps({"sweep_runs": int(nruns), "denoise_steps": int(steps), "seconds": secs,
-                          "steps_per_s": steps / secs if secs else None,
-                          "videos_per_hour": nruns * 3600 / secs if secs else None, "n_gpus": world,
-                          "workers": n_workers, "gpus_per_worker": per}), flush=True)
-    if world > 1:
-        # captured graphs hold the pair communicator: drop them and leave without NCCL's finalizers (see bench.py)
-        for pl in pipe._plans.values():
-            pl.graph = None
-        torch.cuda.synchronize()
-        dist.barrier()
-        import sys
-        sys.stdout.flush()
-        sys.stderr.flush()
-        os._exit(0)
-    return 0
+        from .dist_util import teardown_process_group
+        return teardown_process_group(pipe, ok)
+    return 0 if ok else 1
 
 
 if __name__ == "__main__":

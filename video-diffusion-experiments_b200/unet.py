@@ -377,7 +377,7 @@ class Transformer2DModel(_Packable):
         for blk in self.transformer_blocks[:-1]:
             blk.run(st, h, nimg, hw, last=False)
         hb = self.transformer_blocks[-1].run(st, h, nimg, hw)
-        o.gemm(hb, p["wout"], bias=p["bout"], residual=x, out_f32=x)
+        o.gemm(hb, p["wout"], bias=p["bout"], residual=x, out_f32=x, stats_hw=hw)     # x feeds a GroupNorm next
         return x
 
 
@@ -408,7 +408,7 @@ class AnimateDiffTransformer3D(_Packable):
         for blk in self.transformer_blocks[:-1]:
             blk.run(st, h, nimg, hw, last=False)
         hb = self.transformer_blocks[-1].run(st, h, nimg, hw)
-        o.gemm(hb, p["wout"], bias=p["bout"], residual=x, out_f32=x)
+        o.gemm(hb, p["wout"], bias=p["bout"], residual=x, out_f32=x, stats_hw=hw)     # x feeds a GroupNorm next
         return x
 
     def forward(self, hidden_states, encoder_hidden_states=None, timestep=None, class_labels=None,
@@ -492,13 +492,13 @@ class ResnetBlock2D(_Packable):
         raw = None
         if need_raw:
             a, raw = a
-        h32, _ = o.conv3x3(a, p["w1"], nimg, h, w, bias=p["cb1"], row_bias=temb_proj, rb_div=rb_div)
+        h32, _ = o.conv3x3(a, p["w1"], nimg, h, w, bias=p["cb1"], row_bias=temb_proj, rb_div=rb_div, stats=True)
         a2 = o.group_norm(h32, None, nimg, hw, G, p["g2"], p["b2"], self.norm2.eps, silu=True)
         if need_raw:
             res, _ = o.gemm(raw, p["wsc"], bias=p["bsc"], want_f32=True)
         else:
             res = x
-        out, _ = o.conv3x3(a2, p["w2"], nimg, h, w, bias=p["cb2"], residual=res)
+        out, _ = o.conv3x3(a2, p["w2"], nimg, h, w, bias=p["cb2"], residual=res, stats=True)
         return out
 
     def forward(self, input_tensor, temb, *a, **kw):
@@ -536,7 +536,7 @@ class Downsample2D(_Packable):
     def run(self, st: _State, x, nimg: int, h: int, w: int):
         o, p = st.o, self.packed(st.o)
         s2d = o.cast(x, nimg, h, w, x.shape[1], mode=1)
-        out, _ = o.conv3x3(s2d, p["w"], nimg, h // 2, w // 2, stride2=True, bias=p["b"])
+        out, _ = o.conv3x3(s2d, p["w"], nimg, h // 2, w // 2, stride2=True, bias=p["b"], stats=True)
         return out
 
 
@@ -560,7 +560,7 @@ class Upsample2D(_Packable):
     def run(self, st: _State, x, nimg: int, h: int, w: int):
         o, p = st.o, self.packed(st.o)
         up = o.cast(x, nimg, h, w, x.shape[1], mode=2)
-        out, _ = o.conv3x3(up, p["w"], nimg, 2 * h, 2 * w, bias=p["b"])
+        out, _ = o.conv3x3(up, p["w"], nimg, 2 * h, 2 * w, bias=p["b"], stats=True)
         return out
 
 
@@ -765,8 +765,6 @@ class UNetMotionModel(_Packable):
         self.conv_act = SiLU()
         self.conv_out = Conv2d(boc[0], cfg.out_channels, 3, padding=1)
         self.set_mode(mode)
-        for p in self.parameters():
-            p.requires_grad_(False)
         self.eval()
         self._kv_cache: Optional[Dict[int, torch.Tensor]] = None
         self._kv_cache_key = None
@@ -941,6 +939,7 @@ class UNetMotionModel(_Packable):
         if text_kv is None and (self.module_mode or self._hooks_registered()):
             return self._forward_modules(sample, timestep, encoder_hidden_states)
         o = get_ops(self.mode)
+        o.colstats.clear()
         P = self.packed(o)
         B, cin, F, h, w = sample.shape
         if F > self.cfg.motion_max_seq_length:

@@ -11,7 +11,7 @@ runs a fused plan on channels-last row matrices like the UNet:
       scaling are folded into the 3x3 weights, its bias rides on a ones channel so the zero padding stays exact)
   ResnetBlock2D : GroupNorm+SiLU (b200ad_group_norm) -> tcgen05 implicit-GEMM conv3x3 (+bias) -> GroupNorm+SiLU ->
       conv3x3 (+bias, +fp32 residual / 1x1 shortcut GEMM) -- the UNet's kernels at C = 512/256/128, up to 512^2 pixels
-  mid attention (1 head, d = 512, L = h*w): GroupNorm -> Q|K GEMM -> per image: S = Q K^T (tcgen05 GEMM, fp32 out) ->
+  mid attention (1 head, d = 512, L = h*w): GroupNorm -> Q, K GEMMs -> per image: S = Q K^T (tcgen05 GEMM, fp32 out) ->
       b200ad_softmax_rows -> O = P V (GEMM against V^T, itself produced by a GEMM with swapped operands; V's bias is
       folded into the out-projection bias since softmax rows sum to 1) -> out-projection GEMM (+bias, +residual)
   Upsample2D : nearest x2 written once in the operand type (b200ad_cast mode 2) -> conv3x3
@@ -65,12 +65,12 @@ class _VaeResnet(_Packable):
         raw = None
         if need_raw:
             a, raw = a
-        h32, _ = o.conv3x3(a, p["w1"], n, h, w, bias=p["cb1"])
+        h32, _ = o.conv3x3(a, p["w1"], n, h, w, bias=p["cb1"], stats=True)
         del a
         a2 = o.group_norm(h32, None, n, h * w, G, p["g2"], p["b2"], self.norm2.eps, silu=True)
         del h32
         res = o.gemm(raw, p["wsc"], bias=p["bsc"], want_f32=True)[0] if need_raw else x
-        out, _ = o.conv3x3(a2, p["w2"], n, h, w, bias=p["cb2"], residual=res)
+        out, _ = o.conv3x3(a2, p["w2"], n, h, w, bias=p["cb2"], residual=res, stats=True)
         return out
 
     def forward(self, input_tensor, temb=None, *a, **kw):
@@ -96,8 +96,9 @@ class _VaeAttention(_Packable):
         wo, bo = self.to_out[0].weight.detach().float(), self.to_out[0].bias.detach().float()
         bv = self.to_v.bias.detach().float()
         return {"gn_g": _dev_f(self.group_norm.weight), "gn_b": _dev_f(self.group_norm.bias),
-                "wqk": _dev_w(o, torch.cat([self.to_q.weight.detach(), self.to_k.weight.detach()], 0)),
-                "bqk": _dev_f(torch.cat([self.to_q.bias.detach(), self.to_k.bias.detach()], 0)),
+                "wq": _dev_w(o, self.to_q.weight), "bq": _dev_f(self.to_q.bias),
+                # softmax is invariant to a per-row constant: q.(k + bk) = q.k + q.bk, so K's bias drops out exactly
+                "wk": _dev_w(o, self.to_k.weight),
                 "wv": _dev_w(o, self.to_v.weight),
                 "wo": _dev_w(o, wo),
                 # softmax rows sum to 1: P (V + 1 bv^T) Wo^T + bo = (P V) Wo^T + (Wo bv + bo)
@@ -109,7 +110,8 @@ class _VaeAttention(_Packable):
         C = x.shape[1]
         a = o.group_norm(x, None, n, hw, self.group_norm.num_groups, p["gn_g"], p["gn_b"], self.group_norm.eps,
                          silu=False)
-        _, qk = o.gemm(a, p["wqk"], bias=p["bqk"], want_op=True)                     # [n*hw, 2C]
+        _, q = o.gemm(a, p["wq"], bias=p["bq"], want_op=True)                        # [n*hw, C]
+        _, k = o.gemm(a, p["wk"], want_op=True)
         att = torch.empty((n * hw, C), device=x.device, dtype=o.op_dtype)
         s32 = torch.empty((hw, hw), device=x.device, dtype=torch.float32)
         prob = torch.empty((hw, hw), device=x.device, dtype=o.op_dtype)
@@ -118,10 +120,10 @@ class _VaeAttention(_Packable):
         for i in range(n):
             rows = slice(i * hw, (i + 1) * hw)
             o.gemm(p["wv"], a[rows], out_op=vt)                                       # V^T = Wv A^T   [C, hw]
-            o.gemm(qk[rows, :C], qk[rows, C:], out_f32=s32)                          # S = Q K^T      [hw, hw]
+            o.gemm(q[rows], k[rows], out_f32=s32)                                     # S = Q K^T      [hw, hw]
             o.softmax_rows(s32, scale, out=prob)
             o.gemm(prob, vt, out_op=att[rows])                                        # O = P V        [hw, C]
-        o.gemm(att, p["wo"], bias=p["bo"], residual=x, out_f32=x)
+        o.gemm(att, p["wo"], bias=p["bo"], residual=x, out_f32=x, stats_hw=hw)        # x feeds the next resnet's GroupNorm
         return x
 
     def forward(self, hidden_states, *a, **kw):
@@ -164,7 +166,7 @@ class _VaeUpsample(_Packable):
     def run(self, o: Ops, x, n: int, h: int, w: int):
         p = self.packed(o)
         up = o.cast(x, n, h, w, x.shape[1], mode=2)
-        return o.conv3x3(up, p["w"], n, 2 * h, 2 * w, bias=p["b"])[0]
+        return o.conv3x3(up, p["w"], n, 2 * h, 2 * w, bias=p["b"], stats=True)[0]
 
     def forward(self, x, *a, **kw):
         from . import leaf as _leaf
@@ -221,8 +223,6 @@ class AutoencoderKLDecoder(_Packable):
         self.decoder = _Decoder(chans, groups)
         self.use_slicing = False
         self.frames_per_pass = 16
-        for p in self.parameters():
-            p.requires_grad_(False)
         self.eval()
         self.set_mode(mode)
         self.register_load_state_dict_post_hook(lambda m, keys: m.invalidate_all_packed())
@@ -269,6 +269,7 @@ class AutoencoderKLDecoder(_Packable):
         if not x5.is_cuda:
             raise RuntimeError("AutoencoderKLDecoder: CUDA tensors required (the b200ad path has no CPU fallback)")
         o = get_ops(self.mode)
+        o.colstats.clear()
         P = self.packed(o)
         d = self.decoder
         _, _, n, h, w = x5.shape
