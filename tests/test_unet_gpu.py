@@ -52,6 +52,39 @@ def test_small_unet_matches_oracle(mode, B, F, h, w, t):
     assert e < TOL[mode]
 
 
+@pytest.mark.parametrize("mode", ["bf16", "fp32"])
+@pytest.mark.parametrize("B,F,h,w", [(2, 16, 64, 64), (2, 8, 8, 8), (1, 5, 24, 40), (2, 32, 96, 96)])
+def test_no_read_before_write(mode, B, F, h, w):
+    """Every buffer the kernels' front end allocates is filled with NaN instead of being left uninitialised
+    (ops.POISON): a kernel that reads bytes no kernel of this forward has written -- a statistics slot, a pad column, a
+    tile tail -- turns the noise prediction into NaN instead of silently picking up what the caching allocator last
+    kept there (which made a parity test depend on the tests that ran before it).  Shapes: the benchmarked token
+    counts (64x64), several images per conv tile (8x8), ragged boxes (24x40), config 5's 96x96 x 32 frames."""
+    import b200ad.ops as O
+    from b200ad.unet import UNetMotionConfig as PC, UNetMotionModel
+    from b200ad.vae import AutoencoderKLDecoder
+    torch.manual_seed(0)
+    prod = UNetMotionModel(PC(**SMALL), mode=mode).cuda()
+    lat, txt = _inputs(B, F, h, w)
+    clean = prod(lat.cuda(), 500, encoder_hidden_states=txt.cuda()).sample
+    O.POISON = True
+    try:
+        out = prod(lat.cuda(), 500, encoder_hidden_states=txt.cuda()).sample
+        assert torch.isfinite(out).all(), f"{int((~torch.isfinite(out)).sum())} non-finite outputs: a kernel read unwritten memory"
+        assert torch.equal(out, clean)
+        if (h, w) == (8, 8):
+            vae = AutoencoderKLDecoder((128, 128, 64, 64), mode=mode).cuda()
+            z = torch.randn(1, 4, 3, h, w, device="cuda")
+            img_clean = None
+            O.POISON = False
+            img_clean = vae.decode_video(z)
+            O.POISON = True
+            img = vae.decode_video(z)
+            assert torch.isfinite(img).all() and torch.equal(img, img_clean)
+    finally:
+        O.POISON = False
+
+
 def test_small_unet_text_batch_conventions_and_timestep_forms():
     oracle, prod = _pair(SMALL)
     lat, txt = _inputs(2, 4, 8, 8)
@@ -121,6 +154,27 @@ def test_full_architecture_config2_benchmarked_shape(full_pair):
     oracle, prod = full_pair
     lat, txt = _inputs(2, 16, 64, 64)
     _gate(prod, oracle, lat, txt, 961, "config2 (16f 512^2)", modes=("bf16", "fp32"))
+
+
+@pytest.mark.parametrize("h", [32, 64])
+def test_full_architecture_no_read_before_write(full_pair, h):
+    """ops.POISON (see test_no_read_before_write) on the full architecture at the config-1 / config-2 shapes: the real
+    head widths (40 / 80 / 160 -> attn_fa, attn_x, attn_tc), C = 320 .. 2560 GroupNorm / LayerNorm variants."""
+    import b200ad.ops as O
+    _, prod = full_pair
+    lat, txt = _inputs(2, 16, h, h)
+    for mode in ("bf16", "fp32"):
+        prod.set_mode(mode)
+        clean = prod(lat.cuda(), 961, encoder_hidden_states=txt.cuda()).sample
+        O.POISON = True
+        try:
+            out = prod(lat.cuda(), 961, encoder_hidden_states=txt.cuda()).sample
+        finally:
+            O.POISON = False
+        bad = int((~torch.isfinite(out)).sum())
+        assert bad == 0, f"{mode} {h}x{h}: {bad} non-finite outputs -- a kernel read unwritten memory"
+        assert torch.equal(out, clean), f"{mode} {h}x{h}: result depends on the previous content of its buffers"
+    prod.set_mode("bf16")
 
 
 def test_full_architecture_euler_bf16_one_step(full_pair):

@@ -255,8 +255,12 @@ __global__ void gn_stats_vec_kernel(const float* __restrict__ x0, int c0, const 
     if (s_last) {
       __threadfence();
       const int nblk = gn_nblk(hw);
+      // FULL warps only: the block has R*C/4 threads, which need not be a multiple of 32 (C = 960: 240 threads).  The
+      // trailing partial warp used to take part with warp index nw: it re-did groups warp 0 also owns with half of its
+      // lanes missing (and a full-mask shuffle over them) and raced warp 0 for the same (mean, rstd) slot -- one
+      // image's statistics of four groups came out wrong every few dozen launches (tools/stress_determinism.py).
       const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-      for (int g = warp; g < groups; g += nw) {
+      for (int g = warp; warp < nw && g < groups; g += nw) {
         const float2* base = partial + (long long)n * nblk * groups + g;
         double sd = 0.0, qd = 0.0;
         for (int i = lane; i < nblk; i += 32) {

@@ -15,6 +15,19 @@ from . import lib as _lib
 
 BF16, FP32 = 0, 1
 
+# Diagnostic: POISON = True fills every buffer this module allocates with NaN (0xFF for uint8) instead of leaving it
+# uninitialised, so a kernel that reads bytes no kernel has written yet turns the result into NaN instead of silently
+# picking up whatever the caching allocator last kept there (tests/test_unet_gpu.py::test_no_read_before_write).
+POISON = os.environ.get("B200AD_POISON") == "1"
+
+
+def _empty(shape, device, dtype):
+    if POISON:
+        if dtype in (torch.uint8, torch.int32, torch.int64):
+            return torch.full(tuple(shape), 255 if dtype == torch.uint8 else -1, device=device, dtype=dtype)
+        return torch.full(tuple(shape), float("nan"), device=device, dtype=dtype)
+    return torch.empty(tuple(shape), device=device, dtype=dtype)
+
 
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
@@ -121,14 +134,14 @@ class Ops:
         assert w.shape[1] == K
         n_out = N // 2 if geglu else N
         if want_f32 and out_f32 is None:
-            out_f32 = torch.empty((M, n_out), device=a.device, dtype=torch.float32)
+            out_f32 = _empty((M, n_out), a.device, torch.float32)
         if want_op and out_op is None:
-            out_op = torch.empty((M, n_out), device=a.device, dtype=self.op_dtype)
+            out_op = _empty((M, n_out), a.device, self.op_dtype)
         spi = self._stats_ok(False, stats_hw, 1) if (stats_hw and out_f32 is not None and out_op is None and not geglu
                                                      and M % stats_hw == 0) else 0
         if spi:
             nimg = M // stats_hw
-            st = torch.empty((nimg * spi, N, 2), device=a.device, dtype=torch.float32)
+            st = _empty((nimg * spi, N, 2), a.device, torch.float32)
             with self._rec("gemm", 2.0 * M * N * K, _nb(w, residual, out_f32, st) + M * K * a.element_size()):
                 rc = self.L.b200ad_gemm_stats(
                     self.op, a.data_ptr(), a.stride(0), w.data_ptr(), M, N, K, _ptr(bias), _ptr(row_bias), rb_div,
@@ -158,11 +171,11 @@ class Ops:
         cout, k9 = w.shape
         cin = k9 // 9
         M = nimg * h * wd
-        out_f32 = torch.empty((M, cout), device=src.device, dtype=torch.float32) if want_f32 else None
-        out_op = torch.empty((M, cout), device=src.device, dtype=self.op_dtype) if want_op else None
+        out_f32 = _empty((M, cout), src.device, torch.float32) if want_f32 else None
+        out_op = _empty((M, cout), src.device, self.op_dtype) if want_op else None
         spi = self._stats_ok(True, h, wd) if (stats and want_f32 and not want_op) else 0
         if spi:
-            st = torch.empty((nimg * spi, cout, 2), device=src.device, dtype=torch.float32)
+            st = _empty((nimg * spi, cout, 2), src.device, torch.float32)
             with self._rec("conv3x3", 2.0 * M * cout * k9, _nb(src, w, residual, out_f32, st)):
                 rc = self.L.b200ad_conv3x3_stats(
                     self.op, src.data_ptr(), w.data_ptr(), nimg, h, wd, cin, cout, 1 if stride2 else 0, _ptr(bias),
@@ -183,7 +196,7 @@ class Ops:
         """q/k/v: 2-D operand-typed views (row stride = leading dim).  Returns [nbatch*Lq, heads*d].
         v_ones: pad column d of every head of v holds 1.0 (B200AD_ATTN_V_ONES)."""
         _need_cuda(q, k, v)
-        out = torch.empty((nbatch * Lq, heads * d), device=q.device, dtype=self.op_dtype)
+        out = _empty((nbatch * Lq, heads * d), q.device, self.op_dtype)
         es = out.element_size()
         nbytes = es * heads * d * (2.0 * nbatch * Lq + 2.0 * (nbatch // kv_div) * Lk)
         with self._rec("attention_L%d_d%d" % (Lk, d), 4.0 * nbatch * heads * Lq * Lk * d, nbytes):
@@ -196,7 +209,7 @@ class Ops:
     def temporal_attention(self, qkv, B, F, hw, C, heads):
         _need_cuda(qkv)
         assert qkv.is_contiguous() and qkv.shape == (B * F * hw, 3 * C)
-        out = torch.empty((B * F * hw, C), device=qkv.device, dtype=self.op_dtype)
+        out = _empty((B * F * hw, C), qkv.device, self.op_dtype)
         with self._rec("temporal_attention", 4.0 * B * hw * F * F * C, _nb(qkv, out)):
             rc = self.L.b200ad_temporal_attention(self.op, qkv.data_ptr(), B, F, hw, C, heads, out.data_ptr(),
                                                   _stream())
@@ -212,13 +225,13 @@ class Ops:
         c1 = 0 if x1 is None else x1.shape[-1]
         if x1 is not None:
             assert x1.dtype == torch.float32 and x1.is_contiguous()
-        out = torch.empty((nimg * hw, c0 + c1), device=x0.device, dtype=self.op_dtype)
-        raw = torch.empty_like(out) if want_raw else None
+        out = _empty((nimg * hw, c0 + c1), x0.device, self.op_dtype)
+        raw = _empty(out.shape, out.device, out.dtype) if want_raw else None
         # statistics from the producers' epilogues (every source must have them, for this geometry)
         s0 = self._lookup_stats(x0, nimg, hw, c0)
         s1 = self._lookup_stats(x1, nimg, hw, c1) if x1 is not None else None
         if s0 is not None and (x1 is None or s1 is not None) and (c0 + c1) // groups % 2 == 0 and c0 % 2 == 0:
-            ws = torch.empty((nimg // frames_per_stat * groups, 2), device=x0.device, dtype=torch.float32)
+            ws = _empty((nimg // frames_per_stat * groups, 2), x0.device, torch.float32)
             # algorithmic bytes: the fp32 input ONCE + the operand-typed output(s)
             with self._rec("group_norm", 0.0, _nb(x0, x1) + _nb(out, raw)):
                 rc = self.L.b200ad_gn_apply_stats(
@@ -229,7 +242,7 @@ class Ops:
             _lib.check(rc, "b200ad_gn_apply_stats")
             return (out, raw) if want_raw else out
         nblk = self.L.b200ad_gn_nblk(hw)
-        partial = torch.empty((nimg * nblk * groups + nimg * groups, 2), device=x0.device, dtype=torch.float32)
+        partial = _empty((nimg * nblk * groups + nimg * groups, 2), x0.device, torch.float32)
         # algorithmic bytes (1 read + 1 write is the floor): the fp32 input once + the operand-typed output(s); this
         # path READS the input twice (statistics pass, apply pass)
         with self._rec("group_norm", 0.0, _nb(x0, x1) + _nb(out, raw)):
@@ -249,7 +262,7 @@ class Ops:
         _need_cuda(x)
         assert x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2
         rows, C = x.shape
-        out = torch.empty((rows, C), device=x.device, dtype=self.op_dtype)
+        out = _empty((rows, C), x.device, self.op_dtype)
         with self._rec("layernorm", 0.0, _nb(x, out)):
             rc = self.L.b200ad_layernorm(self.op, x.data_ptr(), rows, C, gamma.data_ptr(), beta.data_ptr(),
                                          float(eps), _ptr(pe), hw, frames, out.data_ptr(), _stream())
@@ -266,7 +279,7 @@ class Ops:
             shape = (4 * nimg * (h // 2) * (w // 2), C)
         else:
             shape = (nimg * 4 * h * w, C)
-        out = torch.empty(shape, device=x.device, dtype=self.op_dtype)
+        out = _empty(shape, x.device, self.op_dtype)
         with self._rec("cast", 0.0, _nb(out) * (1.0 + 4.0 / out.element_size() / (4 if mode == 2 else 1))):
             rc = self.L.b200ad_cast(self.op, x.data_ptr(), nimg, h, w, C, mode, out.data_ptr(), _stream())
         _lib.check(rc, "b200ad_cast")
@@ -276,7 +289,7 @@ class Ops:
     def timestep_sinusoid(self, t, dim):
         _need_cuda(t)
         assert t.dtype == torch.float32 and t.dim() == 1
-        out = torch.empty((t.shape[0], dim), device=t.device, dtype=torch.float32)
+        out = _empty((t.shape[0], dim), t.device, torch.float32)
         _lib.check(self.L.b200ad_timestep_sinusoid(t.data_ptr(), t.shape[0], dim, out.data_ptr(), _stream()),
                    "b200ad_timestep_sinusoid")
         return out
@@ -286,7 +299,7 @@ class Ops:
         assert x.dtype == torch.float32 and w.dtype == torch.float32 and x.is_contiguous() and w.is_contiguous()
         M, K = x.shape
         N = w.shape[0]
-        y = torch.empty((M, N), device=x.device, dtype=torch.float32)
+        y = _empty((M, N), x.device, torch.float32)
         with self._rec("small_linear", 2.0 * M * N * K, _nb(w, x, y)):
             _lib.check(self.L.b200ad_small_linear(x.data_ptr(), M, K, w.data_ptr(), _ptr(b), N, int(silu_in),
                                                   int(silu_out), y.data_ptr(), _stream()), "b200ad_small_linear")
@@ -297,7 +310,7 @@ class Ops:
         assert sample.dtype == torch.float32 and sample.is_contiguous() and sample.dim() == 5
         B, cin, F, h, wd = sample.shape
         cout = w.shape[0]
-        out = torch.empty((B * F * h * wd, cout), device=sample.device, dtype=torch.float32)
+        out = _empty((B * F * h * wd, cout), sample.device, torch.float32)
         with self._rec("conv_in", 2.0 * B * F * h * wd * cout * cin * 9, _nb(sample, out)):
             _lib.check(self.L.b200ad_conv_in(sample.data_ptr(), B, cin, F, h, wd, w.data_ptr(), _ptr(b), cout,
                                              out.data_ptr(), _stream()), "b200ad_conv_in")
@@ -307,7 +320,7 @@ class Ops:
         _need_cuda(act, w)
         cout, cin = w.shape[0], w.shape[1]
         assert act.dtype == self.op_dtype and act.is_contiguous()
-        out = torch.empty((B, cout, F, h, wd), device=act.device, dtype=torch.float32)
+        out = _empty((B, cout, F, h, wd), act.device, torch.float32)
         with self._rec("conv_out", 2.0 * B * F * h * wd * cout * cin * 9, _nb(act, out)):
             _lib.check(self.L.b200ad_conv_out(self.op, act.data_ptr(), B, F, h, wd, cin, w.data_ptr(), _ptr(b), cout,
                                               out.data_ptr(), _stream()), "b200ad_conv_out")
@@ -323,7 +336,7 @@ class Ops:
         _need_cuda(x)
         assert x.dtype == torch.float32 and x.is_contiguous()
         with self._rec("eltwise", 0.0, 2 * _nb(x)):
-            return self._eltwise(0, x, None, x.numel(), 1, 1, torch.empty_like(x))
+            return self._eltwise(0, x, None, x.numel(), 1, 1, _empty(x.shape, x.device, x.dtype))
 
     def add(self, a, b, div: int = 1, mod=None):
         """a + b.flat[(i // div) % mod] (mod defaults to b.numel(): plain add when b has a's size)."""
@@ -332,14 +345,14 @@ class Ops:
         mod = b.numel() if mod is None else mod
         assert mod <= b.numel() and (div != 1 or mod != b.numel() or b.numel() <= a.numel())
         with self._rec("eltwise", 0.0, 2 * _nb(a) + _nb(b)):
-            return self._eltwise(1, a, b, a.numel(), div, mod, torch.empty_like(a))
+            return self._eltwise(1, a, b, a.numel(), div, mod, _empty(a.shape, a.device, a.dtype))
 
     def geglu_gate(self, hg):
         """[rows, 2C] = (h | g) -> [rows, C] = h * gelu_erf(g)."""
         _need_cuda(hg)
         assert hg.dtype == torch.float32 and hg.is_contiguous() and hg.dim() == 2 and hg.shape[1] % 2 == 0
         rows, c2 = hg.shape
-        out = torch.empty((rows, c2 // 2), device=hg.device, dtype=torch.float32)
+        out = _empty((rows, c2 // 2), hg.device, torch.float32)
         with self._rec("eltwise", 0.0, _nb(hg, out)):
             return self._eltwise(2, hg, None, out.numel(), 1, c2 // 2, out)
 
@@ -349,7 +362,7 @@ class Ops:
         assert s.dtype == torch.float32 and s.dim() == 2 and s.stride(1) == 1
         rows, cols = s.shape
         if out is None:
-            out = torch.empty((rows, cols), device=s.device, dtype=self.op_dtype)
+            out = _empty((rows, cols), s.device, self.op_dtype)
         with self._rec("softmax_rows", 0.0, rows * cols * (4.0 + out.element_size())):
             _lib.check(self.L.b200ad_softmax_rows(self.op, s.data_ptr(), rows, cols, s.stride(0), float(scale),
                                                   out.data_ptr(), out.stride(0), _stream()), "b200ad_softmax_rows")
@@ -360,7 +373,7 @@ class Ops:
         _need_cuda(video)
         assert video.dtype == torch.float32 and video.is_contiguous() and video.dim() == 4
         C, F, h, w = video.shape
-        out = torch.empty((F, h, w, C), device=video.device, dtype=torch.uint8)
+        out = _empty((F, h, w, C), video.device, torch.uint8)
         with self._rec("video_to_u8", 0.0, _nb(video, out)):
             _lib.check(self.L.b200ad_video_to_u8(video.data_ptr(), C, F, h, w, out.data_ptr(), _stream()),
                        "b200ad_video_to_u8")
@@ -374,7 +387,7 @@ class Ops:
         B, cin, F, h, wd = sample.shape
         cout = w_aug.shape[0]
         assert w_aug.shape[1] == cin + 1
-        out = torch.empty((B * F * h * wd, cout), device=sample.device, dtype=torch.float32)
+        out = _empty((B * F * h * wd, cout), sample.device, torch.float32)
         with self._rec("conv_in", 2.0 * B * F * h * wd * cout * (cin + 1) * 9, _nb(sample, out)):
             _lib.check(self.L.b200ad_conv_in_affine(sample.data_ptr(), B, cin, F, h, wd, w_aug.data_ptr(), _ptr(b), cout,
                                                     out.data_ptr(), _stream()), "b200ad_conv_in_affine")
@@ -387,7 +400,7 @@ class Ops:
             assert t.dtype == torch.float32 and t.is_contiguous()
         n = latents.numel()
         if latents_out is None:
-            latents_out = torch.empty_like(latents)
+            latents_out = _empty(latents.shape, latents.device, latents.dtype)
         copies = 0 if model_in is None else model_in.numel() // n
         _lib.check(self.L.b200ad_cfg_step(eps_u.data_ptr(), eps_c.data_ptr(), latents.data_ptr(), float(g),
                                           float(cx), float(ce), float(in_scale), n, latents_out.data_ptr(),

@@ -28,7 +28,7 @@ import torch
 import torch.nn as nn
 
 from .leaf import Conv2d, GroupNorm, Linear, SiLU
-from .ops import Ops, get_ops
+from .ops import Ops, _empty, get_ops
 from .unet import _Packable, _dev_f, _dev_w, _mode_of, _pack_conv3x3
 
 
@@ -112,10 +112,10 @@ class _VaeAttention(_Packable):
                          silu=False)
         _, q = o.gemm(a, p["wq"], bias=p["bq"], want_op=True)                        # [n*hw, C]
         _, k = o.gemm(a, p["wk"], want_op=True)
-        att = torch.empty((n * hw, C), device=x.device, dtype=o.op_dtype)
-        s32 = torch.empty((hw, hw), device=x.device, dtype=torch.float32)
-        prob = torch.empty((hw, hw), device=x.device, dtype=o.op_dtype)
-        vt = torch.empty((C, hw), device=x.device, dtype=o.op_dtype)
+        att = _empty((n * hw, C), x.device, o.op_dtype)
+        s32 = _empty((hw, hw), x.device, torch.float32)
+        prob = _empty((hw, hw), x.device, o.op_dtype)
+        vt = _empty((C, hw), x.device, o.op_dtype)
         scale = float(C) ** -0.5
         for i in range(n):
             rows = slice(i * hw, (i + 1) * hw)
