@@ -37,7 +37,7 @@ FRAMES, LAT_H, LAT_W, NUM_STEPS, GUIDANCE = 16, 64, 64, 25, 7.5
 FLOPS_PER_STEP = 35.498e12          # SURVEY.md Appendix C, algorithmic FLOPs of one CFG step at this shape
 # N > 1 layout when --layout auto: "pairs" = CFG-split GPU pairs (BASELINE configs[2], north star), "replicas" =
 # independent single-GPU videos.  Both are measured (profiles/); the faster one is the default.
-DEFAULT_LAYOUT = {2: "pairs", 4: "pairs", 8: "pairs"}
+DEFAULT_LAYOUT = {2: "pairs", 4: "replicas", 8: "replicas"}
 
 
 def _peaks():

@@ -176,13 +176,24 @@ class FrameExporter:
     def _export_async(self, host, ev, run, exp_dir):
         ev.synchronize()
         arr = host.numpy()
-        # frames in parallel on the pool's other threads, GIF here; the marker after all of them
-        futs = [self.pool.submit(self._timed, _encode_png, arr[i], exp_dir / "frames" / f"frame_{i:04d}.png")
+        # per frame, on the pool's other threads: the PNG, and the palette quantisation of the GIF frame (PIL's GIF
+        # writer spends ~90 % of its time there; pre-quantised "P" frames give a byte-identical file); then the GIF is
+        # assembled here and the marker written after every file of the run is on disk
+        pngs = [self.pool.submit(self._timed, _encode_png, arr[i], exp_dir / "frames" / f"frame_{i:04d}.png")
                 for i in range(arr.shape[0])]
-        self._timed(_encode_gif, arr, exp_dir / f"{run.experiment_id}.gif")
-        for f in futs:
+        quant = [self.pool.submit(self._timed_ret, _quantize_frame, arr[i]) for i in range(arr.shape[0])]
+        frames = [q.result() for q in quant]
+        self._timed(_save_gif, frames, exp_dir / f"{run.experiment_id}.gif")
+        for f in pngs:
             f.result()
         _write_marker(run, exp_dir)
+
+    def _timed_ret(self, fn, *a):
+        t0 = time.perf_counter()
+        r = fn(*a)
+        with self.lock:
+            self.encode_seconds += time.perf_counter() - t0
+        return r
 
     def finish(self):
         t0 = time.perf_counter()
@@ -199,10 +210,18 @@ def _encode_png(frame, path):
     Image.fromarray(frame).save(path)
 
 
-def _encode_gif(arr, path):
+def _quantize_frame(frame):
+    """RGB -> 256-colour adaptive palette, exactly the conversion PIL's GIF writer applies to an RGB frame."""
     from PIL import Image
-    frames = [Image.fromarray(f) for f in arr]
+    return Image.fromarray(frame).convert("P", palette=Image.Palette.ADAPTIVE)
+
+
+def _save_gif(frames, path):
     frames[0].save(os.fspath(path), save_all=True, append_images=frames[1:], optimize=False, duration=100, loop=0)
+
+
+def _encode_gif(arr, path):
+    _save_gif([_quantize_frame(f) for f in arr], path)          # same bytes as export_to_gif(frames, path) (05:181-182)
 
 
 def _encode_run(arr, run, exp_dir):
@@ -300,7 +319,8 @@ def main(argv=None) -> int:
     ap.add_argument("--limit", type=int, default=0, help="only the first LIMIT runs (smoke runs)")
     ap.add_argument("--sync-export", action="store_true",
                     help="encode PNG/GIF synchronously between videos, as the reference does (05:172-190)")
-    ap.add_argument("--export-threads", type=int, default=4)
+    ap.add_argument("--export-threads", type=int, default=0,
+                    help="encoder threads per writer rank (0: host cores / ranks on this node, at least 3)")
     ap.add_argument("--height", type=int, default=HEIGHT)
     ap.add_argument("--width", type=int, default=WIDTH)
     a = ap.parse_args(argv)
@@ -342,6 +362,8 @@ def main(argv=None) -> int:
     pipe.scheduler = DDIMScheduler.from_config(pipe.scheduler.config, beta_schedule="linear", steps_offset=1,
                                                clip_sample=False)                             # 05:136-141
     pipe.cfg_group = group
+    if a.export_threads <= 0:
+        a.export_threads = max(3, (os.cpu_count() or 8) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", world))))
     ok = False
     try:
         stats = run_worker(pipe, mine, out_dir, writer=(rank % per == 0), decode=not a.latent_only,
@@ -366,6 +388,7 @@ def main(argv=None) -> int:
                               "workers": n_workers, "gpus_per_worker": per,
                               "layout": "pairs" if per == 2 else "replicas", "decode": not a.latent_only,
                               "export": "synchronous" if a.sync_export else f"overlapped ({a.export_threads} threads)",
+                              "host_cores": os.cpu_count(),
                               "sum_over_workers": {k: round(v, 3) for k, v in tot.items() if k.endswith("seconds")},
                               "what": "wall clock of the slowest worker from its first video to its last marker on disk: "
                                       "denoise loop + VAE decode + uint8 + PNG x16 + GIF + config.json per run"}),
