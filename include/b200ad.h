@@ -167,9 +167,21 @@ int b200ad_conv_in_affine(const float* sample, int B, int cin, int F, int h, int
 /* ---- module-mode glue (the hook-visible eager mode: one diffusers sub-module = one call).
  * mode 0: out[i] = silu(a[i]) (nn.SiLU);  mode 1: out[i] = a[i] + b[(i / div) % mod] (residual add: div = 1, mod = n;
  * timestep-embedding add over NCHW: div = h*w, mod = N*C; positional-embedding add: div = 1, mod = F*C);
- * mode 2: GEGLU gate, a = [rows, 2C] (h | g), n = rows*C, mod = C: out[rows, C] = h * gelu_erf(g). */
+ * mode 2: GEGLU gate, a = [rows, 2C] (h | g), n = rows*C, mod = C: out[rows, C] = h * gelu_erf(g);
+ * mode 3: out[i] = a[i] * sigmoid(1.702 a[i])  (CLIP's quick_gelu). */
 int b200ad_eltwise(int mode, const float* a, const float* b, long long n, long long div, long long mod, float* out,
                    void* stream);
+
+/* ---- f2: CLIP text encoder pieces (replaces transformers' CLIPTextModel under AnimateDiffPipeline.encode_prompt, loaded
+ * at 05_grid_search_ablation.py:130-134).  embed_tokens: out[t,:] = token_table[ids[t],:] + position_table[t % seq,:]
+ * (fp32).  attention_small: softmax(q k^T / sqrt(d) [+ causal mask]) v for short sequences (77 tokens), head h of batch
+ * item n at q[(n*L + i)*ldq + h*d + j]; operand-typed in and out.  The projections / MLP run on b200ad_gemm, the
+ * LayerNorms on b200ad_layernorm, quick_gelu on b200ad_eltwise mode 3. */
+int b200ad_embed_tokens(const long long* ids, long long ntok, int seq, int vocab, const float* tok_table,
+                        const float* pos_table, int dim, float* out, void* stream);
+int b200ad_attention_small(int op_dtype, const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                           long long ldv, int nbatch, int heads, int L, int d, int causal, void* out_op, long long ldo,
+                           void* stream);
 
 /* ---- row softmax of an fp32 score matrix into the operand type: out[r, :] = softmax(scale * s[r, :]), cols <= 8192,
  * cols % 4 == 0 (VAE decoder mid-block attention, 1 head of d = 512: S = Q K^T by b200ad_gemm, this, P V by b200ad_gemm;

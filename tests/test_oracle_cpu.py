@@ -164,3 +164,29 @@ def test_oracle_golden_fixture():
     final = denoise_loop(m, sch, lat, txt, g["guidance"], g["steps"])
     assert abs(final.double().pow(2).sum().item() - g["final_sumsq"]) / g["final_sumsq"] < 5e-4
     assert sch.timesteps.tolist() == g["timesteps"]
+
+
+def test_oracle_clip_text_matches_transformers():
+    """Row f2's oracle is PINNED: transformers (the reference's own dependency for the text encoder,
+    /root/reference/requirements.txt:7) is importable here, so the restatement is compared with the library's
+    CLIPTextModel on identical random-init weights and token ids."""
+    transformers = pytest.importorskip("transformers")
+    from oracle.clip_text import ClipTextConfig, make_oracle_clip
+    cfg = ClipTextConfig(num_hidden_layers=3)                    # 3 of the 12 identical layers keep the CPU test short
+    o = make_oracle_clip(seed=2, cfg=cfg, round_to=None)
+    tc = transformers.CLIPTextConfig(hidden_size=768, intermediate_size=3072, num_hidden_layers=3,
+                                     num_attention_heads=12, max_position_embeddings=77, vocab_size=49408,
+                                     hidden_act="quick_gelu")
+    m = transformers.CLIPTextModel(tc).eval()
+    res = m.load_state_dict(o.state_dict(), strict=False)
+    assert not res.unexpected_keys and all(k.endswith("position_ids") for k in res.missing_keys)
+    ids = torch.randint(0, 49408, (2, 77), generator=torch.Generator().manual_seed(0))
+    with torch.no_grad():
+        ref = m(ids)[0]
+    out = o(ids)
+    assert out.shape == (2, 77, 768)
+    assert ((out - ref).norm() / ref.norm()).item() < 1e-5
+    # causal: the embedding of token i does not depend on later tokens
+    ids2 = ids.clone()
+    ids2[:, 40:] = 7
+    assert torch.allclose(o(ids2)[:, :40], out[:, :40], atol=1e-5)

@@ -11,14 +11,80 @@
 
 namespace b200ad {
 
-// mode 0: out[i] = silu(a[i]);  mode 1: out[i] = a[i] + b[(i / div) % mod]
+// mode 0: out[i] = silu(a[i]);  mode 1: out[i] = a[i] + b[(i / div) % mod];  mode 3: quick_gelu, a * sigmoid(1.702 a)
 __global__ void eltwise_kernel(int mode, const float* __restrict__ a, const float* __restrict__ b, long long n,
                                long long div, long long mod, float* __restrict__ out) {
   pdl_enter();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const float v = a[i];
-    out[i] = mode == 0 ? silu_f(v) : v + b[(i / div) % mod];
+    out[i] = mode == 0 ? silu_f(v) : (mode == 3 ? v / (1.0f + expf(-1.702f * v)) : v + b[(i / div) % mod]);
+  }
+}
+
+// CLIP text embeddings: out[t, :] = token_table[ids[t], :] + position_table[t % seq, :]
+__global__ void embed_tokens_kernel(const long long* __restrict__ ids, long long ntok, int seq, int vocab,
+                                    const float* __restrict__ tok, const float* __restrict__ pos, int dim,
+                                    float* __restrict__ out) {
+  pdl_enter();
+  const long long n = ntok * dim;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const long long t = i / dim;
+    const int c = (int)(i % dim);
+    long long id = ids[t];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    out[i] = tok[id * dim + c] + pos[(t % seq) * (long long)dim + c];
+  }
+}
+
+// Short-sequence attention with an optional causal mask (CLIP text encoder: 77 tokens, 12 heads of 64): one warp per
+// (batch item, head, query row); lanes split the keys for the scores and the head width for P V.  fp32 math.
+template <typename T>
+__global__ void __launch_bounds__(128) attn_small_kernel(const T* __restrict__ q, long long ldq, const T* __restrict__ k,
+                                                         long long ldk, const T* __restrict__ v, long long ldv, int heads,
+                                                         int L, int d, int causal, T* __restrict__ out, long long ldo,
+                                                         long long nrows) {
+  pdl_enter();
+  extern __shared__ float sm_attn[];              // [warps][d] query row + [warps][L] probabilities
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const long long w = (long long)blockIdx.x * nw + warp;     // (n * heads + h) * L + i
+  if (w >= nrows) return;
+  const int i = (int)(w % L);
+  const int h = (int)((w / L) % heads);
+  const long long n = w / ((long long)L * heads);
+  float* sq = sm_attn + (size_t)warp * d;
+  float* sp = sm_attn + (size_t)nw * d + (size_t)warp * L;
+  const float scale = rsqrtf((float)d);
+  const T* qr = q + (n * L + i) * ldq + (long long)h * d;
+  for (int c = lane; c < d; c += 32) sq[c] = to_f<T>(qr[c]) * scale;
+  __syncwarp();
+  const int nk = causal ? i + 1 : L;
+  float mx = -INFINITY;
+  for (int j = lane; j < nk; j += 32) {
+    const T* kr = k + (n * L + j) * ldk + (long long)h * d;
+    float s = 0.f;
+    for (int c = 0; c < d; ++c) s = fmaf(sq[c], to_f<T>(kr[c]), s);
+    sp[j] = s;
+    mx = fmaxf(mx, s);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float sum = 0.f;
+  for (int j = lane; j < nk; j += 32) {
+    const float p = __expf(sp[j] - mx);
+    sp[j] = p;
+    sum += p;
+  }
+  sum = warp_sum(sum);
+  __syncwarp();
+  const float inv = 1.0f / sum;
+  T* orow = out + (n * L + i) * ldo + (long long)h * d;
+  for (int c = lane; c < d; c += 32) {
+    float acc = 0.f;
+    for (int j = 0; j < nk; ++j) acc = fmaf(sp[j], to_f<T>(v[(n * L + j) * ldv + (long long)h * d + c]), acc);
+    if (sizeof(T) == 2) orow[c] = (T)__float2bfloat16(acc * inv);
+    else *reinterpret_cast<float*>(orow + c) = acc * inv;
   }
 }
 
@@ -129,8 +195,8 @@ extern "C" int b200ad_eltwise(int mode, const float* a, const float* b, long lon
     pdl_launch(geglu_gate_kernel, dim3(grid_for(n, 256)), dim3(256), (size_t)0, (cudaStream_t)stream, a, n / mod, (int)mod,
                out);
   } else {
-    B200AD_REQUIRE(mode == 0 || mode == 1, "eltwise: mode %d", mode);
-    B200AD_REQUIRE(mode == 0 || (b && div > 0 && mod > 0), "eltwise(add): needs b, div > 0, mod > 0");
+    B200AD_REQUIRE(mode == 0 || mode == 1 || mode == 3, "eltwise: mode %d", mode);
+    B200AD_REQUIRE(mode != 1 || (b && div > 0 && mod > 0), "eltwise(add): needs b, div > 0, mod > 0");
     pdl_launch(eltwise_kernel, dim3(grid_for(n, 256)), dim3(256), (size_t)0, (cudaStream_t)stream, mode, a, b, n,
                div > 0 ? div : 1, mod > 0 ? mod : 1, out);
   }
@@ -162,6 +228,36 @@ extern "C" int b200ad_video_to_u8(const float* video_cfhw, int C, int F, int h, 
   const long long npix = (long long)F * h * w;
   pdl_launch(video_to_u8_kernel, dim3(grid_for(npix, 256)), dim3(256), (size_t)0, (cudaStream_t)stream, video_cfhw, C, F, h,
              w, (uint8_t*)out_fhwc);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200ad_embed_tokens(const long long* ids, long long ntok, int seq, int vocab, const float* tok_table,
+                                   const float* pos_table, int dim, float* out, void* stream) {
+  B200AD_REQUIRE(ids && tok_table && pos_table && out && seq > 0 && dim > 0 && vocab > 0, "embed_tokens: bad arguments");
+  pdl_launch(embed_tokens_kernel, dim3(grid_for(ntok * dim, 256)), dim3(256), (size_t)0, (cudaStream_t)stream, ids, ntok, seq,
+             vocab, tok_table, pos_table, dim, out);
+  count_launch();
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200ad_attention_small(int op_dtype, const void* q, long long ldq, const void* k, long long ldk,
+                                      const void* v, long long ldv, int nbatch, int heads, int L, int d, int causal,
+                                      void* out_op, long long ldo, void* stream) {
+  B200AD_REQUIRE(q && k && v && out_op, "attention_small: null operand");
+  B200AD_REQUIRE(L >= 1 && L <= 1024 && d >= 1 && d <= 256, "attention_small: L=%d d=%d unsupported", L, d);
+  const int nw = 4;
+  const long long nrows = (long long)nbatch * heads * L;
+  const size_t smem = (size_t)nw * (d + L) * sizeof(float);
+  const unsigned blocks = (unsigned)((nrows + nw - 1) / nw);
+  if (op_dtype == 0)
+    pdl_launch(attn_small_kernel<bf16>, dim3(blocks), dim3(nw * 32), smem, (cudaStream_t)stream, (const bf16*)q, ldq,
+               (const bf16*)k, ldk, (const bf16*)v, ldv, heads, L, d, causal, (bf16*)out_op, ldo, nrows);
+  else
+    pdl_launch(attn_small_kernel<float>, dim3(blocks), dim3(nw * 32), smem, (cudaStream_t)stream, (const float*)q, ldq,
+               (const float*)k, ldk, (const float*)v, ldv, heads, L, d, causal, (float*)out_op, ldo, nrows);
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -45,6 +45,8 @@ SIGNATURES = {
     "b200ad_conv_out": [_I, _P, _I, _I, _I, _I, _I, _P, _P, _I, _P, _P],
     "b200ad_conv_in_affine": [_P, _I, _I, _I, _I, _I, _P, _P, _I, _P, _P],
     "b200ad_eltwise": [_I, _P, _P, _L, _L, _L, _P, _P],
+    "b200ad_embed_tokens": [_P, _L, _I, _I, _P, _P, _I, _P, _P],
+    "b200ad_attention_small": [_I, _P, _L, _P, _L, _P, _L, _I, _I, _I, _I, _I, _P, _L, _P],
     "b200ad_softmax_rows": [_I, _P, _L, _I, _L, _F, _P, _L, _P],
     "b200ad_video_to_u8": [_P, _I, _I, _I, _I, _P, _P],
     "b200ad_cfg_step": [_P, _P, _P, _F, _F, _F, _F, _L, _P, _P, _I, _P],

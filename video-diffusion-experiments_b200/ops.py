@@ -347,6 +347,33 @@ class Ops:
         with self._rec("eltwise", 0.0, 2 * _nb(a) + _nb(b)):
             return self._eltwise(1, a, b, a.numel(), div, mod, _empty(a.shape, a.device, a.dtype))
 
+    def quick_gelu(self, x):
+        _need_cuda(x)
+        assert x.dtype == torch.float32 and x.is_contiguous()
+        with self._rec("eltwise", 0.0, 2 * _nb(x)):
+            return self._eltwise(3, x, None, x.numel(), 1, 1, _empty(x.shape, x.device, x.dtype))
+
+    def embed_tokens(self, ids, tok_table, pos_table):
+        """ids int64 [B, seq] -> fp32 [B*seq, dim] = token_table[ids] + position_table[:seq]."""
+        _need_cuda(ids, tok_table, pos_table)
+        assert ids.dtype == torch.int64 and ids.is_contiguous() and tok_table.is_contiguous() and pos_table.is_contiguous()
+        B, seq = ids.shape
+        dim = tok_table.shape[1]
+        out = _empty((B * seq, dim), ids.device, torch.float32)
+        _lib.check(self.L.b200ad_embed_tokens(ids.data_ptr(), B * seq, seq, tok_table.shape[0], tok_table.data_ptr(),
+                                              pos_table.data_ptr(), dim, out.data_ptr(), _stream()), "b200ad_embed_tokens")
+        return out
+
+    def attention_small(self, q, k, v, nbatch, heads, L, d, causal=False):
+        """Short-sequence attention (optionally causal) on 2-D operand-typed views -> [nbatch*L, heads*d]."""
+        _need_cuda(q, k, v)
+        out = _empty((nbatch * L, heads * d), q.device, self.op_dtype)
+        with self._rec("attention_small", 4.0 * nbatch * heads * L * L * d, _nb(out) * 4):
+            _lib.check(self.L.b200ad_attention_small(self.op, q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0),
+                                                     v.data_ptr(), v.stride(0), nbatch, heads, L, d, 1 if causal else 0,
+                                                     out.data_ptr(), out.stride(0), _stream()), "b200ad_attention_small")
+        return out
+
     def geglu_gate(self, hg):
         """[rows, 2C] = (h | g) -> [rows, C] = h * gelu_erf(g)."""
         _need_cuda(hg)

@@ -110,7 +110,8 @@ def _load_checked(module, sd: dict, what: str, allow_missing=lambda k: False, al
 class _LocalClip:
     """CLIP ViT-L/14 text encoder + tokenizer from a LOCAL diffusers-layout directory (``text_encoder/``,
     ``tokenizer/``), as AnimateDiffPipeline loads them at /root/reference/experiments/05_grid_search_ablation.py:130-134.
-    Off the denoise path: runs once per prompt through transformers' CLIPTextModel."""
+    The encoder runs on the b200ad kernels (clip.py), once per prompt; the tokenizer is transformers'
+    CLIPTokenizer (host-side string processing)."""
 
     def __init__(self, tokenizer, model):
         self.tokenizer, self.model = tokenizer, model
@@ -119,7 +120,7 @@ class _LocalClip:
     def __call__(self, prompt: str) -> torch.Tensor:
         ids = self.tokenizer(prompt, padding="max_length", max_length=self.tokenizer.model_max_length,
                              truncation=True, return_tensors="pt").input_ids
-        return self.model(ids.to(self.model.device))[0].float()          # [1, 77, 768]
+        return self.model(ids.cuda()).float()                              # [1, 77, 768]
 
 
 def _load_text_encoder(path: str):
@@ -128,12 +129,11 @@ def _load_text_encoder(path: str):
         _log(f"'{path}': no local text_encoder/ + tokenizer/ -> prompts map to synthetic text embeddings "
              "(seeded by the prompt string)")
         return None
-    from transformers import CLIPTextModel, CLIPTokenizer
+    from transformers import CLIPTokenizer
+    from .clip import CLIPTextEncoder
     tok = CLIPTokenizer.from_pretrained(tk, local_files_only=True)
-    model = CLIPTextModel.from_pretrained(te, local_files_only=True).eval()
-    if torch.cuda.is_available():
-        model = model.cuda()
-    _log(f"'{path}': CLIP text encoder loaded from the local directory")
+    model = CLIPTextEncoder.from_local(te)
+    _log(f"'{path}': CLIP text encoder loaded from the local directory (b200ad kernels)")
     return _LocalClip(tok, model)
 
 

@@ -378,6 +378,9 @@ def main(argv=None) -> int:
             dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
             t[0] = tmax[0]
+        # the collectives only order the STREAMS: wait for them on the host, so that rank 0 lists the markers after every
+        # rank has finished exporting (the first 8-GPU run's manifest missed the last run of seven workers)
+        t = t.cpu()
         if rank == 0:
             generate_manifest(out_dir)
             secs = float(t[0])
