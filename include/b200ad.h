@@ -193,6 +193,33 @@ int b200ad_softmax_rows(int op_dtype, const float* s, long long rows, int cols, 
  * round(clamp(x/2 + 0.5, 0, 1) * 255)  (the frames consumed at 05_grid_search_ablation.py:169,178-179). */
 int b200ad_video_to_u8(const float* video_cfhw, int C, int F, int h, int w, unsigned char* out_fhwc, void* stream);
 
+/* ---- f4: temporal-consistency metrics of a generated video (replaces the CPU loops of the reference's
+ * experiments/06_measure_grid_search.py:209-284,290-352).  frames: uint8 [F, H, W, C] on the device (what
+ * b200ad_video_to_u8 writes).  workspace: b200ad_metric_blocks() * 3 * (F-1) doubles.
+ *  video_pair_sums: out[2*i] = sum over the frame of (I_i - I_{i+1})^2, out[2*i+1] = sum |I_i - 2 I_{i+1} + I_{i+2}|
+ *    (0 for the last pair), i < F-1, in uint8 units, exact integers (-> compute_mse / compute_psnr / compute_flicker_index).
+ *  video_warp_error: flow [F-1, H, W, 2] fp32 (dx, dy); out[3*i] = sum (warp(I_i, flow_i) - I_{i+1})^2 in [0,1] units
+ *    (warp_frame: bilinear, border padding, align_corners=True), out[3*i+1] = sum |flow_i|, out[3*i+2] = sum |flow_i|^2.
+ *  video_gray_u8: the uint8 luminance handed to OpenCV's Farneback flow (06:163-164). */
+int b200ad_metric_blocks(void);
+int b200ad_video_pair_sums(const unsigned char* frames_fhwc, int F, long long n_per_frame, double* workspace, double* out,
+                           void* stream);
+int b200ad_video_warp_error(const unsigned char* frames_fhwc, int F, int H, int W, int C, const float* flow,
+                            double* workspace, double* out, void* stream);
+int b200ad_video_gray_u8(const unsigned char* frames_fhwc, long long npix, int C, unsigned char* gray, void* stream);
+
+/* LPIPS (AlexNet) between consecutive frames (replaces lpips.LPIPS(net='alex') at 06:101-131): lpips_input applies the
+ * [0,255] -> [-1,1] map and LPIPS' ScalingLayer; conv2d_direct is an fp32 direct convolution over NHWC (weights
+ * [cout, kh, kw, cin], any kernel / stride / padding, bias, optional ReLU: AlexNet's 11x11 s4, 5x5 and 3x3 layers);
+ * maxpool2d = MaxPool2d(ks, stride); lpips_layer: out[i] = sum over pixels of sum_c lin[c] (f_i/|f_i| - f_{i+1}/|f_{i+1}|)^2
+ * for the features [N, hw, C] of N consecutive frames (the caller divides by hw and adds the five layers). */
+int b200ad_lpips_input(const unsigned char* frames_nhwc, long long n_elems, float* out, void* stream);
+int b200ad_conv2d_direct(const float* x_nhwc, int N, int H, int W, int Cin, const float* w_ohwi, const float* bias,
+                         int Cout, int KH, int KW, int stride, int pad, int relu, float* out_nhwc, void* stream);
+int b200ad_maxpool2d(const float* x_nhwc, int N, int H, int W, int C, int ks, int stride, float* out_nhwc, void* stream);
+int b200ad_lpips_layer(const float* feat_nhwc, int N, int hw, int C, const float* lin, double* workspace, double* out,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif

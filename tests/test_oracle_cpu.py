@@ -190,3 +190,36 @@ def test_oracle_clip_text_matches_transformers():
     ids2 = ids.clone()
     ids2[:, 40:] = 7
     assert torch.allclose(o(ids2)[:, :40], out[:, :40], atol=1e-5)
+
+
+def test_oracle_metrics_known_answers():
+    """Row f4's oracle (the reference's formulas, 06:209-284): closed-form cases."""
+    from oracle import metrics as OM
+    a = torch.rand(3, 16, 20)
+    assert OM.compute_mse(a, a) == 0.0 and OM.compute_psnr(0.0) == 100.0
+    assert abs(OM.compute_psnr(0.01) - 20.0) < 1e-9
+    ramp = torch.stack([torch.full((3, 8, 8), 0.1 * t) for t in range(5)])          # linear in time: no flicker
+    assert OM.compute_flicker_index(ramp) < 1e-7
+    osc = torch.stack([torch.full((3, 8, 8), float(t % 2)) for t in range(5)])      # 0,1,0,1,0: |0-2+0| = 2
+    assert abs(OM.compute_flicker_index(osc) - 2.0) < 1e-7
+    import numpy as np
+    assert torch.allclose(OM.warp_frame(a, np.zeros((16, 20, 2), np.float32)), a, atol=1e-6)
+    shift = np.zeros((16, 20, 2), np.float32)
+    shift[..., 0] = 1.0                                                             # sample one pixel to the right
+    w = OM.warp_frame(a, shift)
+    assert torch.allclose(w[:, :, :-1], a[:, :, 1:], atol=1e-5) and torch.allclose(w[:, :, -1], a[:, :, -1], atol=1e-5)
+
+
+def test_oracle_lpips_alexnet_geometry_matches_torchvision():
+    tv = pytest.importorskip("torchvision")
+    from oracle.lpips_alex import ALEX_CONVS, make_oracle_lpips, lpips_consecutive
+    feats = tv.models.alexnet(weights=None).features
+    for sl, idx, cin, cout, k, s, p, pool in ALEX_CONVS:
+        c = feats[idx]
+        assert (c.in_channels, c.out_channels, c.kernel_size[0], c.stride[0], c.padding[0]) == (cin, cout, k, s, p)
+        assert isinstance(feats[idx + 1], torch.nn.ReLU) and (not pool or isinstance(feats[idx - 1], torch.nn.MaxPool2d))
+    m = make_oracle_lpips()
+    fr = torch.rand(3, 3, 64, 64, generator=torch.Generator().manual_seed(0))
+    d = lpips_consecutive(m, fr)
+    assert len(d) == 2 and all(v > 0 for v in d)
+    assert lpips_consecutive(m, torch.stack([fr[0], fr[0]]))[0] == 0.0

@@ -49,6 +49,14 @@ SIGNATURES = {
     "b200ad_attention_small": [_I, _P, _L, _P, _L, _P, _L, _I, _I, _I, _I, _I, _P, _L, _P],
     "b200ad_softmax_rows": [_I, _P, _L, _I, _L, _F, _P, _L, _P],
     "b200ad_video_to_u8": [_P, _I, _I, _I, _I, _P, _P],
+    "b200ad_metric_blocks": [],
+    "b200ad_video_pair_sums": [_P, _I, _L, _P, _P, _P],
+    "b200ad_video_warp_error": [_P, _I, _I, _I, _I, _P, _P, _P, _P],
+    "b200ad_video_gray_u8": [_P, _L, _I, _P, _P],
+    "b200ad_lpips_input": [_P, _L, _P, _P],
+    "b200ad_conv2d_direct": [_P, _I, _I, _I, _I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P],
+    "b200ad_maxpool2d": [_P, _I, _I, _I, _I, _I, _I, _P, _P],
+    "b200ad_lpips_layer": [_P, _I, _I, _I, _P, _P, _P, _P],
     "b200ad_cfg_step": [_P, _P, _P, _F, _F, _F, _F, _L, _P, _P, _I, _P],
     "b200ad_cfg_step_dev": [_P, _P, _P, _P, _L, _P, _P, _I, _P],
 }
