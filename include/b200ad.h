@@ -81,9 +81,10 @@ int b200ad_group_norm(int op_dtype, const float* x0, int c0, const float* x1, in
 /* ---- K6 without the statistics pass: the producing GEMM / conv emits per-(32-row slot, column) sums of its fp32
  * output from its epilogue (b200ad_gemm_stats / b200ad_conv3x3_stats: float2 col_stats[(image*spi + k)*N + col], spi =
  * b200ad_stats_slots(conv, h, w) slots per image), and b200ad_gn_apply_stats reduces them (tiny) and applies: the
- * GroupNorm reads its input ONCE.  meanrstd_ws: (nimg/frames_per_stat)*groups float2 of workspace.  Same module
+ * GroupNorm reads its input ONCE.  meanrstd_ws: b200ad_gn_stats_ws_bytes(nimg, groups, frames_per_stat) bytes, 16-byte aligned.  Same module
  * replacements as K6 / K1 / K2; the stats entry points write the fp32 output only. */
 int b200ad_stats_slots(int conv, int h, int w);
+long long b200ad_gn_stats_ws_bytes(int nimg, int groups, int frames_per_stat);
 int b200ad_gemm_stats(int op_dtype, const void* A, long long lda, const void* W, int M, int N, int K,
                       const float* bias, const float* row_bias, int rb_div, int ld_rb, const float* residual,
                       long long ld_res, float* out_f32, long long ld_o32, float* col_stats, int rows_per_image,

@@ -121,11 +121,16 @@ static void conv_box(int h, int w, int* nb, int* hb, int* wb) {
 }
 
 int b200ad_stats_slots(int conv, int h, int w) {
-  if (!conv) return (h * w) % 32 == 0 ? (h * w) / 32 : -1;
+  if (!conv) {
+    const int hw = h * w;
+    if (hw % 32 != 0) return -1;
+    const int mq = hw % 128 == 0 ? 4 : (hw % 64 == 0 ? 2 : 1);      // 32-row quarters of a tile merged per slot
+    return hw / (32 * mq);
+  }
   int nb, hb, wb;
   conv_box(h, w, &nb, &hb, &wb);
   if (hb * wb < 32) return -1;
-  return ((w + wb - 1) / wb) * ((h + hb - 1) / hb) * (hb * wb / 32);
+  return ((w + wb - 1) / wb) * ((h + hb - 1) / hb);                // one slot per image and tile
 }
 
 static int conv_impl(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout, int mode,

@@ -519,8 +519,7 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   // measured (profiles/kbench_attention_variants_r01.txt, L=4096 d=40, V ones column): with one issuer warp per query
   // tile, P in tensor memory and a 5-stage K/V ring the anti-phase start gives 1.62 ms against 1.71 ms without
   // (it was a loss with the single in-order issuer) -> on by default
-  static const int stagger = getenv("B200AD_FA_STAGGER") ? atoi(getenv("B200AD_FA_STAGGER")) : 1;
-  p.stagger = stagger;
+  p.stagger = 1;
   p.dbg = g_fa_dbg;
   p.dk16 = (d + 15) / 16;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)d);
@@ -548,36 +547,16 @@ int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk
                       long long ldo, cudaStream_t stream) {
   if (Lq != Lk || kv_div != 1 || Lq % 256 != 0 || Lq < 512) return 1;
   const bool vs = v_ones && d < dpad;
-  // A/B switch for kbench.  Two threads per row measured no faster than one (1.91 vs 1.87 ms at L=4096 d=40): the
-  // loop is not latency-bound, so the simpler variant stays the default.
-  static const int tpr = getenv("B200AD_FA_TPR") ? atoi(getenv("B200AD_FA_TPR")) : 1;
-  // P in tensor memory (tcgen05.st + A-from-TMEM PV MMA): 1.71 vs 1.87 ms at L=4096 d=40, 223 vs 229 us at L=1024 d=80
-  static const int pt = getenv("B200AD_FA_PT") ? atoi(getenv("B200AD_FA_PT")) : 1;
-#define FA_LAUNCH(DPV, BNV)                                                                                         \
-  do {                                                                                                              \
-    if (tpr == 1 && pt)                                                                                             \
-      return vs ? launch_attn_fa<DPV, BNV, true, 1, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)  \
-                : launch_attn_fa<DPV, BNV, false, 1, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream); \
-    if (tpr == 1)                                                                                                   \
-      return vs ? launch_attn_fa<DPV, BNV, true, 1, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)  \
-                : launch_attn_fa<DPV, BNV, false, 1, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream); \
-    return vs ? launch_attn_fa<DPV, BNV, true, 2, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)    \
-              : launch_attn_fa<DPV, BNV, false, 2, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);  \
-  } while (0)
-  // three query tiles per CTA (d <= 64 only: TMEM holds 3 x (S 64 + O 64 + P 32) columns)
-  // measured at L=4096 d=40 (profiles/kbench_attention_variants_r01.txt): 1.56 vs 1.62-1.70 ms with the V ones
-  // column, but 1.74-1.85 vs 1.66-1.71 ms with the explicit row sum -> three tiles only with the ones column
-  static const int nt_env = getenv("B200AD_FA_NT") ? atoi(getenv("B200AD_FA_NT")) : 0;
-  const int nt = nt_env ? nt_env : (vs ? 3 : 2);
-  if (dpad == 64 && nt == 2 && tpr == 2 && pt)
-    return vs ? launch_attn_fa<64, 128, true, 2, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
-              : launch_attn_fa<64, 128, false, 2, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
-  if (dpad == 64 && nt == 3 && tpr == 1 && pt)
+  // Instantiated: the variants that measured fastest (profiles/kbench_attention_variants_r01.txt keeps the numbers of
+  // the ones that did not -- two softmax threads per row, P through shared memory, speculative exponentials, other tile
+  // counts; their launch paths and environment switches are gone).  One softmax thread per row, P in tensor memory;
+  // d <= 64 with the V ones column: three query tiles per CTA (1.56 vs 1.62-1.70 ms at L=4096 d=40), else two.
+  if (dpad == 64)
     return vs ? launch_attn_fa<64, 64, true, 1, true, 3>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
-              : launch_attn_fa<64, 64, false, 1, true, 3>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
-  if (dpad == 64) FA_LAUNCH(64, 128);
-  if (dpad == 128) FA_LAUNCH(128, 64);
-#undef FA_LAUNCH
+              : launch_attn_fa<64, 128, false, 1, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
+  if (dpad == 128)
+    return vs ? launch_attn_fa<128, 64, true, 1, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
+              : launch_attn_fa<128, 64, false, 1, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
   return 1;
 }
 

@@ -320,8 +320,7 @@ static int launch_attn_x(const void* q, long long ldq, const void* k, long long 
 int attention_bf16_x(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                      int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div, void* out, long long ldo,
                      cudaStream_t stream) {
-  static const int on = getenv("B200AD_ATTN_X") ? atoi(getenv("B200AD_ATTN_X")) : 1;
-  if (!on || Lk > 128 || d % 8 != 0 || ldo % 8 != 0 || (reinterpret_cast<uintptr_t>(out) & 15)) return 1;
+  if (Lk > 128 || d % 8 != 0 || ldo % 8 != 0 || (reinterpret_cast<uintptr_t>(out) & 15)) return 1;
 #define AX_LAUNCH(DPV)                                                                                              \
   do {                                                                                                              \
     if (Lk <= 80)                                                                                                   \

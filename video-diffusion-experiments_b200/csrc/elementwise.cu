@@ -87,36 +87,37 @@ __global__ void gn_finalize_kernel(const float2* __restrict__ partial, int nblk,
   }
 }
 
-// (mean, rstd) per (statistic, group) from the per-(32-row slot, column) sums the producing GEMM / conv epilogue
-// emitted (gemm_tc.cu STATS): float2 st[(image*spi + k)*c + col].  The input is the channel concatenation of up to two
-// tensors with their own statistics buffers.  One block per (statistic, group); fixed summation order (fp32 per thread,
-// fp64 across threads), so the result is deterministic.
-__global__ void __launch_bounds__(256) gn_finalize_colstats_kernel(const float2* __restrict__ st0, int c0, int spi0,
+// Group statistics from the per-(slot, column) sums the producing GEMM / conv epilogue emitted (gemm_tc.cu STATS):
+// float2 st[(image*spi + k)*c + col].  The input is the channel concatenation of up to two tensors with their own
+// statistics buffers.  One block per (image, group) sums that image's slots x the group's channels (fixed order: fp32
+// per thread, fp64 across threads => deterministic).  frames_per_stat == 1: writes (mean, rstd) at once; otherwise (the
+// motion module: statistics over all frames of a batch item) writes the image's (sum, sum of squares) as doubles and
+// gn_combine_frames_kernel adds the frames_per_stat images of a statistic -- one block per (statistic, group) over all
+// frames took 57 us at level 0 (64 blocks, 20480 elements each), per image it is a few microseconds.
+__global__ void __launch_bounds__(128) gn_finalize_colstats_kernel(const float2* __restrict__ st0, int c0, int spi0,
                                                                    const float2* __restrict__ st1, int c1, int spi1,
                                                                    int groups, int frames_per_stat, int hw, float eps,
-                                                                   float2* __restrict__ meanrstd) {
+                                                                   float2* __restrict__ meanrstd,
+                                                                   double2* __restrict__ img_sums) {
   pdl_enter();
-  __shared__ double red_s[8], red_q[8];
-  const int stat = blockIdx.y, g = blockIdx.x;
+  __shared__ double red_s[4], red_q[4];
+  const int img = blockIdx.y, g = blockIdx.x;
   const int C = c0 + c1, cpg = C / groups;
   const int ch0 = g * cpg, ch1 = ch0 + cpg;
   double s = 0.0, q = 0.0;
-  // the group's channels inside source 0 / source 1
   for (int src = 0; src < 2; ++src) {
     const float2* st = src ? st1 : st0;
     const int cs = src ? c1 : c0, off = src ? c0 : 0, spi = src ? spi1 : spi0;
     if (!st) continue;
-    const int a = max(ch0, off) - off, b = min(ch1, off + cs) - off;
+    const int a = max(ch0, off) - off, b = min(ch1, off + cs) - off;      // the group's channels inside this source
     if (b <= a) continue;
     const int wd = b - a;
-    const long long slots = (long long)frames_per_stat * spi;
-    const float2* base = st + ((long long)stat * slots) * cs + a;
-    const long long total = slots * wd;
+    const float2* base = st + ((long long)img * spi) * cs + a;
+    const int total = spi * wd;
     float fs = 0.f, fq = 0.f;
-    for (long long i = threadIdx.x; i < total; i += blockDim.x) {
-      const long long sl = i / wd;
-      const int ch = (int)(i - sl * wd);
-      const float2 v = __ldg(base + sl * cs + ch);
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+      const int sl = i / wd, ch = i - sl * wd;
+      const float2 v = __ldg(base + (long long)sl * cs + ch);
       fs += v.x; fq += v.y;
     }
     s += fs; q += fq;
@@ -130,14 +131,36 @@ __global__ void __launch_bounds__(256) gn_finalize_colstats_kernel(const float2*
   if (lane == 0) { red_s[warp] = s; red_q[warp] = q; }
   __syncthreads();
   if (threadIdx.x == 0) {
-    s = 0.0; q = 0.0;
-    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { s += red_s[w]; q += red_q[w]; }
-    const double cnt = (double)frames_per_stat * hw * cpg;
-    const double mean = s / cnt;
-    double var = q / cnt - mean * mean;
-    if (var < 0.0) var = 0.0;
-    meanrstd[stat * groups + g] = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)eps)));
+    s = (red_s[0] + red_s[1]) + (red_s[2] + red_s[3]);
+    q = (red_q[0] + red_q[1]) + (red_q[2] + red_q[3]);
+    if (frames_per_stat == 1) {
+      const double cnt = (double)hw * cpg;
+      const double mean = s / cnt;
+      double var = q / cnt - mean * mean;
+      if (var < 0.0) var = 0.0;
+      meanrstd[img * groups + g] = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)eps)));
+    } else {
+      img_sums[img * groups + g] = make_double2(s, q);
+    }
   }
+}
+
+__global__ void gn_combine_frames_kernel(const double2* __restrict__ img_sums, int nstat, int groups, int frames_per_stat,
+                                         int hw, int cpg, float eps, float2* __restrict__ meanrstd) {
+  pdl_enter();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nstat * groups) return;
+  const int stat = i / groups, g = i % groups;
+  double s = 0.0, q = 0.0;
+  for (int f = 0; f < frames_per_stat; ++f) {
+    const double2 v = img_sums[(stat * frames_per_stat + f) * groups + g];
+    s += v.x; q += v.y;
+  }
+  const double cnt = (double)frames_per_stat * hw * cpg;
+  const double mean = s / cnt;
+  double var = q / cnt - mean * mean;
+  if (var < 0.0) var = 0.0;
+  meanrstd[i] = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)eps)));
 }
 
 template <typename T>
@@ -427,9 +450,8 @@ static constexpr int GN_MAX_COUNTERS = 8192;
 // is in progress (cudaMalloc is illegal there): the caller then keeps the separate finalize kernel.
 static unsigned int* gn_counters(cudaStream_t st) {
   static unsigned int* buf[16] = {};
-  static const bool on = !(getenv("B200AD_GN_FUSED_FIN") && atoi(getenv("B200AD_GN_FUSED_FIN")) == 0);
   int dev = -1;
-  if (!on || cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
   if (!buf[dev]) {
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return nullptr;
@@ -475,8 +497,7 @@ static int gn_stats_launch(const float* x0, int c0, const float* x1, int c1, int
     const dim3 vgrid((gn_nblk(hw) + GN_SB - 1) / GN_SB, nimg);
     // the ticket counters must be zero when the kernel starts: clear them in stream order (a residue -- e.g. from a
     // launch on another stream that overlapped this one -- would make an image finalize early on stale partial sums)
-    static const bool ticket_memset = !(getenv("B200AD_GN_TICKET_MEMSET") && atoi(getenv("B200AD_GN_TICKET_MEMSET")) == 0);
-    if (counters && GN_SB == 1 && ticket_memset)
+    if (counters && GN_SB == 1)
       B200AD_CHECK_CUDA(cudaMemsetAsync(counters, 0, (size_t)nimg * sizeof(unsigned int), (cudaStream_t)stream));
     if (counters && GN_SB == 1)
       pdl_launch(gn_stats_vec_kernel<true>, dim3(vgrid), dim3(R * (C / 4)), (size_t)R * C * sizeof(float2), (cudaStream_t)stream,
@@ -527,7 +548,9 @@ static int gn_apply_launch(int op_dtype, const float* x0, int c0, const float* x
         part, nblk, frames_per_stat, groups, hw, C / groups, eps, meanrstd, nstat);
     count_launch();
   }
-  static const bool persist = !(getenv("B200AD_GN_PERSIST") && atoi(getenv("B200AD_GN_PERSIST")) == 0);
+  // measured (tools/kbench.py norm): the persistent kernel wins on the large level-0 tensors (68.7 vs 73.0 us at
+  // 32 x 64^2 x 320) and loses on the small ones (45.1 vs 43.8 us at 32^2 x 640, 31.7 vs 28.3 us at 16^2 x 1280)
+  const bool persist = (double)nimg * hw * C * 4.0 >= 128e6;
   if (gn_vec_ok(C, c0, groups) && persist) {
     const int R = gn_vec_R(C);
     const int threads = R * (C / 4);
@@ -572,6 +595,12 @@ static int gn_apply_launch(int op_dtype, const float* x0, int c0, const float* x
   return 0;
 }
 
+extern "C" long long b200ad_gn_stats_ws_bytes(int nimg, int groups, int frames_per_stat) {
+  const long long nstat = nimg / (frames_per_stat > 0 ? frames_per_stat : 1);
+  const long long mr = ((nstat * groups + 1) & ~1LL) * (long long)sizeof(float2);
+  return mr + (frames_per_stat > 1 ? (long long)nimg * groups * (long long)sizeof(double2) : 0);
+}
+
 // GroupNorm whose statistics come from the producer's epilogue: finalize (tiny) + apply; the fp32 input is read ONCE.
 extern "C" int b200ad_gn_apply_stats(int op_dtype, const float* x0, int c0, const float* st0, int spi0,
                                      const float* x1, int c1, const float* st1, int spi1, int nimg, int hw, int groups,
@@ -584,18 +613,27 @@ extern "C" int b200ad_gn_apply_stats(int op_dtype, const float* x0, int c0, cons
   B200AD_REQUIRE(frames_per_stat >= 1 && nimg % frames_per_stat == 0, "gn_apply_stats: nimg=%d frames_per_stat=%d", nimg,
                  frames_per_stat);
   const int nstat = nimg / frames_per_stat;
-  pdl_launch(gn_finalize_colstats_kernel, dim3(groups, nstat), dim3(256), (size_t)0, (cudaStream_t)stream,
+  // workspace: [nstat*groups] float2 (mean, rstd), then (frames_per_stat > 1) [nimg*groups] double2 image sums
+  float2* mr = reinterpret_cast<float2*>(meanrstd_ws);
+  double2* sums = reinterpret_cast<double2*>(mr + (((size_t)nstat * groups + 1) & ~(size_t)1));
+  pdl_launch(gn_finalize_colstats_kernel, dim3(groups, nimg), dim3(128), (size_t)0, (cudaStream_t)stream,
              reinterpret_cast<const float2*>(st0), c0, spi0, reinterpret_cast<const float2*>(st1), c1, spi1, groups,
-             frames_per_stat, hw, eps, reinterpret_cast<float2*>(meanrstd_ws));
+             frames_per_stat, hw, eps, mr, sums);
   count_launch();
+  if (frames_per_stat > 1) {
+    const int n = nstat * groups;
+    pdl_launch(gn_combine_frames_kernel, dim3((n + 127) / 128), dim3(128), (size_t)0, (cudaStream_t)stream,
+               (const double2*)sums, nstat, groups, frames_per_stat, hw, C / groups, eps, mr);
+    count_launch();
+  }
   B200AD_CHECK_CUDA(cudaGetLastError());
   return gn_apply_launch(op_dtype, x0, c0, x1, c1, nimg, hw, groups, nullptr, frames_per_stat, eps, gamma, beta, silu,
                          out_op, raw_op, stream, false, reinterpret_cast<const float2*>(meanrstd_ws));
 }
 
-// Fused GroupNorm: statistics + finalize + apply in one call (same workspace layout as gn_stats/gn_apply).  Optionally
-// (B200AD_GN_L2_WALK) walked over sub-batches of images that fit the L2, so that the apply pass re-reads its input
-// from L2 instead of HBM.
+// Fused GroupNorm: statistics + finalize + apply in one call (same workspace layout as gn_stats/gn_apply).  (A walk
+// over L2-sized sub-batches measured slower -- 145 vs 106 us at 32 x 64^2 x 320, profiles/kbench_r01j.txt -- and is gone;
+// the two-pass path itself now only serves inputs whose producer emits no column statistics: conv_in's output.)
 extern "C" int b200ad_group_norm(int op_dtype, const float* x0, int c0, const float* x1, int c1, int nimg, int hw,
                                  int groups, float* partial, int frames_per_stat, float eps, const float* gamma,
                                  const float* beta, int silu, void* out_op, void* raw_op, void* stream) {
@@ -603,19 +641,7 @@ extern "C" int b200ad_group_norm(int op_dtype, const float* x0, int c0, const fl
   const int C = c0 + c1;
   B200AD_REQUIRE(frames_per_stat >= 1 && nimg % frames_per_stat == 0, "group_norm: nimg=%d frames_per_stat=%d", nimg,
                  frames_per_stat);
-  const double img_bytes = (double)hw * C * 4.0;
-  const double budget = 56e6;                       // fp32 input bytes per sub-batch (its bf16 output shares the L2)
-  int chunk = nimg;
-  // Measured on B200 (profiles/kbench_r01j.txt): the sub-batched walk is SLOWER than two whole-tensor passes
-  // (145 vs 106 us at 32 x 64^2 x 320: eight small launch triples do not fill the machine and pay launch gaps), so
-  // it stays opt-in for experiments.
-  static const bool l2_walk = getenv("B200AD_GN_L2_WALK") != nullptr;
-  if (l2_walk && img_bytes * nimg > 72e6) {
-    chunk = (int)(budget / img_bytes);
-    if (chunk < frames_per_stat) chunk = frames_per_stat;
-    chunk -= chunk % frames_per_stat;
-    if (chunk > nimg) chunk = nimg;
-  }
+  const int chunk = nimg;
   const int nblk = gn_nblk(hw);
   const size_t esz = op_dtype == 0 ? 2 : 4;
   // per-call layout of `partial`: [nimg*nblk*groups] float2 partial sums, then [nimg*groups] float2 (mean, rstd);

@@ -63,8 +63,9 @@ struct TcParams {
   long long* dbg;              // optional [grid][16] cycle counters (b200ad_debug_buffer), null in production
   // GroupNorm column statistics of the fp32 output (STATS instantiations): float2 [(image*spi + k)*N + col]
   float2* stats;
-  int stats_spi;               // 32-row slots per image
-  int stats_qpi;               // conv: slots per image inside one tile (h_box*w_box/32); dense: unused
+  int stats_spi;               // statistic slots per image
+  int stats_mq;                // 32-row quarters of a tile merged into one slot (4: the whole tile lies in one image)
+  int off_stat;                // smem: [2 groups][MAX_NBUF][4 quarters][32 columns] float2 hand-over to the I/O warp
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -458,6 +459,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const TileCoord t = tile_coord(p, tile, rank);
       const int nchunks = tile_chunks(p, t.n_tile);
       const int ocol0 = (t.n_tile * p.BN) >> (f_geglu ? 1 : 0);
+      // column statistics: element offset (slot * N) of the up to four slots this tile feeds, -1 = no such image / rows
+      const int st_mq = STATS ? p.stats_mq : 4;
+      long long st_off[4] = {-1, -1, -1, -1};
+      if (STATS) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (j * st_mq >= 4) continue;
+          if (p.conv) {
+            const int img = t.n0 + j;
+            if (img < p.nimg) st_off[j] = ((long long)img * p.stats_spi + (t.m_tile % (p.tiles_x * p.tiles_y))) * p.N;
+          } else {
+            const long long row0 = (long long)t.m_tile * BM + j * 32 * st_mq;
+            if (row0 < p.M) st_off[j] = (row0 / (32 * st_mq)) * p.N;
+          }
+        }
+      }
       for (int c = 0; c < nchunks; ++c) {
         const int g = (c + io_it) & 1;
         IoGroup& G = g ? G1 : G0;
@@ -477,6 +494,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (f_oop) tma_store_2d(&em.oop, ob, ocol, t.m_tile * BM);
           }
           tma_store_commit();
+        }
+        if (STATS) {
+          // (after the chunk's TMA store is on its way) lane = column of the chunk: merge the quarters that belong to
+          // one image and store one float2 per slot and column
+          const uint32_t sa = smem_u32(smem + p.off_stat) + (uint32_t)((((g * MAX_NBUF + G.buf) * 4) * 32 + lane) * 8);
+          float2 qs[4];
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq)
+            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(qs[qq].x), "=f"(qs[qq].y) : "r"(sa + (uint32_t)(qq * 256)));
+          float2* col = p.stats + (t.n_tile * p.BN + c * 32 + lane);
+          if (st_mq == 4) {
+            if (st_off[0] >= 0) col[st_off[0]] = make_float2((qs[0].x + qs[1].x) + (qs[2].x + qs[3].x), (qs[0].y + qs[1].y) + (qs[2].y + qs[3].y));
+          } else if (st_mq == 2) {
+            if (st_off[0] >= 0) col[st_off[0]] = make_float2(qs[0].x + qs[1].x, qs[0].y + qs[1].y);
+            if (st_off[1] >= 0) col[st_off[1]] = make_float2(qs[2].x + qs[3].x, qs[2].y + qs[3].y);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (st_off[j] >= 0) col[st_off[j]] = qs[j];
+          }
+        }
+        if (io_lane) {
           const long long i2 = prof_clock();
           io_issue += i2 - i1;
           // the store of this group's previous chunk is the 2nd (or, at an odd tile boundary, the 1st) most recent
@@ -544,25 +583,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       // column statistics: which rows of this warp's quarter exist, and the slot they are summed into
       uint32_t st_mask = 0;
-      float2* st_row = nullptr;
       if (STATS) {
         bool valid;
-        long long slot;
-        bool slot_ok;
         if (p.conv) {
           const int x = t.x0 + (r % p.w_box), y = t.y0 + ((r / p.w_box) % p.h_box);
           const int n = t.n0 + r / (p.w_box * p.h_box);
           valid = x < p.w && y < p.h && n < p.nimg;
-          const int img = t.n0 + quarter / p.stats_qpi;
-          slot_ok = img < p.nimg;
-          slot = (long long)img * p.stats_spi + (t.m_tile % (p.tiles_x * p.tiles_y)) * p.stats_qpi + quarter % p.stats_qpi;
         } else {
           valid = (long long)t.m_tile * BM + r < p.M;
-          slot = (long long)t.m_tile * 4 + quarter;
-          slot_ok = (long long)t.m_tile * BM + quarter * 32 < p.M;
         }
         st_mask = __ballot_sync(0xffffffffu, valid);
-        if (slot_ok) st_row = p.stats + slot * p.N + t.n_tile * p.BN + lane;
       }
       const long long q0 = prof_clock();
       const float* bias_t = p.bias ? p.bias + t.n_tile * p.BN : nullptr;
@@ -656,7 +686,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             s0 += x0; q0_ = fmaf(x0, x0, q0_);
             s1 += x1; q1_ = fmaf(x1, x1, q1_);
           }
-          if (st_row) st_row[c * 32] = make_float2(s0 + s1, q0_ + q1_);
+          // hand the quarter's column sums to the I/O warp, which merges the quarters of one image and stores them
+          const uint32_t sa = smem_u32(smem + p.off_stat) + (uint32_t)((((g * MAX_NBUF + buf) * 4 + quarter) * 32 + lane) * 8);
+          asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(sa), "f"(s0 + s1), "f"(q0_ + q1_) : "memory");
         }
         fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the TMA store
         mbar_arrive(&cdone[buf]);
@@ -782,14 +814,15 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   if (p.stats) {
     B200AD_REQUIRE(e.out_f32 && !e.geglu, "gemm: column statistics need an fp32 output");
     if (g.enabled) {
-      p.stats_qpi = g.h_box * g.w_box / 32;
-      B200AD_REQUIRE(p.stats_qpi >= 1, "conv: column statistics need >= 32 pixels of one image per tile (box %dx%dx%d)",
+      p.stats_mq = g.h_box * g.w_box / 32;                 // = 4 / n_box: quarters of one image inside a tile
+      B200AD_REQUIRE(p.stats_mq >= 1, "conv: column statistics need >= 32 pixels of one image per tile (box %dx%dx%d)",
                      g.n_box, g.h_box, g.w_box);
-      p.stats_spi = p.tiles_x * p.tiles_y * p.stats_qpi;
+      p.stats_spi = p.tiles_x * p.tiles_y;
     } else {
       B200AD_REQUIRE(e.stats_hw > 0 && e.stats_hw % 32 == 0 && a.M % e.stats_hw == 0,
                      "gemm: column statistics need rows per image (%d) to be a multiple of 32 dividing M=%d", e.stats_hw, a.M);
-      p.stats_spi = e.stats_hw / 32;
+      p.stats_mq = e.stats_hw % 128 == 0 ? 4 : (e.stats_hw % 64 == 0 ? 2 : 1);
+      p.stats_spi = e.stats_hw / (32 * p.stats_mq);
     }
   }
   p.num_m_pairs = (num_m_tiles + 1) / 2;
@@ -810,7 +843,8 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   if (p.has_oop) if (int rc = make_out_map(&em.oop, e.out_op, e.ld_oop, n_out, 2, a)) return rc;
   // ---- shared memory plan: mainloop stages first, the rest goes to epilogue chunk buffers (bytes in flight)
   const int per_buf = ((p.has_res || p.has_o32) ? F32_BUF_BYTES : 0) + (p.has_oop ? OP_BUF_BYTES : 0);
-  const int fixed = 2 * 256 * 4 + 512;                       // bias staging + barriers
+  const int stat_bytes = p.stats ? 2 * MAX_NBUF * 4 * 32 * 8 : 0;       // quarter sums handed to the I/O warp
+  const int fixed = 2 * 256 * 4 + 512 + stat_bytes;          // bias staging + barriers (+ statistics hand-over)
   const int budget = SMEM_LIMIT - 1024 - fixed;
   int want_stages = p.num_kb < 6 ? (p.num_kb < 3 ? 3 : p.num_kb) : 6;
   {
@@ -841,13 +875,13 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
   p.off_f32 = p.num_stages * p.stage_bytes;
   p.off_op = p.off_f32 + ((p.has_res || p.has_o32) ? 2 * p.nbuf * F32_BUF_BYTES : 0);
   p.off_bias = p.off_op + (p.has_oop ? 2 * p.nbuf * OP_BUF_BYTES : 0);
-  p.off_bars = p.off_bias + 2 * 256 * 4;
+  p.off_stat = p.off_bias + 2 * 256 * 4;
+  p.off_bars = p.off_stat + stat_bytes;
   const size_t smem_bytes = (size_t)p.off_bars + 512 + 1024 /*align*/;
   B200AD_REQUIRE(smem_bytes <= (size_t)SMEM_LIMIT, "gemm: %zu bytes of shared memory", smem_bytes);
-  static const bool epi_generic = getenv("B200AD_GEMM_EPI_GENERIC") != nullptr;      // A/B switch: run-time flags only
   const int epi_mask = (p.geglu ? 8 : 0) | (p.has_res ? 4 : 0) | (p.has_o32 ? 2 : 0) | (p.has_oop ? 1 : 0);
   // instantiated: operand only (1), fp32 only (2), residual + operand (5), residual + fp32 (6), all three (7), GEGLU (9)
-  const bool epi_known = !epi_generic && (epi_mask == 1 || epi_mask == 2 || epi_mask == 5 || epi_mask == 6 ||
+  const bool epi_known = (epi_mask == 1 || epi_mask == 2 || epi_mask == 5 || epi_mask == 6 ||
                                           epi_mask == 7 || epi_mask == 9);
   if (!g_attr_set) {
     B200AD_CHECK_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<-1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));

@@ -27,6 +27,7 @@ SIGNATURES = {
     "b200ad_conv3x3": [_I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _I, _I, _P, _L, _P, _L, _P, _L, _P],
     "b200ad_gn_nblk": [_I],
     "b200ad_stats_slots": [_I, _I, _I],
+    "b200ad_gn_stats_ws_bytes": [_I, _I, _I],
     "b200ad_gemm_stats": [_I, _P, _L, _P, _I, _I, _I, _P, _P, _I, _I, _P, _L, _P, _L, _P, _I, _P],
     "b200ad_conv3x3_stats": [_I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _I, _I, _P, _L, _P, _L, _P, _P],
     "b200ad_gn_apply_stats": [_I, _P, _I, _P, _I, _P, _I, _P, _I, _I, _I, _I, _I, _F, _P, _P, _I, _P, _P, _P, _P],
@@ -60,7 +61,7 @@ SIGNATURES = {
     "b200ad_cfg_step": [_P, _P, _P, _F, _F, _F, _F, _L, _P, _P, _I, _P],
     "b200ad_cfg_step_dev": [_P, _P, _P, _P, _L, _P, _P, _I, _P],
 }
-_RESTYPES = {"b200ad_last_error": c_char_p, "b200ad_launch_count": c_longlong}
+_RESTYPES = {"b200ad_last_error": c_char_p, "b200ad_launch_count": c_longlong, "b200ad_gn_stats_ws_bytes": c_longlong}
 
 
 class B200ADError(RuntimeError):

@@ -231,7 +231,7 @@ class Ops:
         s0 = self._lookup_stats(x0, nimg, hw, c0)
         s1 = self._lookup_stats(x1, nimg, hw, c1) if x1 is not None else None
         if s0 is not None and (x1 is None or s1 is not None) and (c0 + c1) // groups % 2 == 0 and c0 % 2 == 0:
-            ws = _empty((nimg // frames_per_stat * groups, 2), x0.device, torch.float32)
+            ws = _empty((int(self.L.b200ad_gn_stats_ws_bytes(nimg, groups, frames_per_stat)) // 8,), x0.device, torch.float64)
             # algorithmic bytes: the fp32 input ONCE + the operand-typed output(s)
             with self._rec("group_norm", 0.0, _nb(x0, x1) + _nb(out, raw)):
                 rc = self.L.b200ad_gn_apply_stats(
