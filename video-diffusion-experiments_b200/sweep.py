@@ -264,14 +264,20 @@ def worker_layout(world: int, pair: bool):
 
 
 def run_worker(pipe, my_runs: Sequence[ExperimentConfig], output_dir: Path, writer: bool, decode: bool = True,
-               log=print, sync_export: bool = False, export_threads: int = 4) -> dict:
+               log=print, sync_export: bool = False, export_threads: int = 4, metrics_dir: Optional[Path] = None) -> dict:
     """Walk one worker's list the way the reference's loops do (generate -> save -> marker).  In a CFG pair both
     ranks run the denoise loop (they stay in lock-step through the per-step all-gather); only `writer` decodes the
     latents (b200ad VAE -> uint8 frames on the device) and exports, overlapped with the next video (FrameExporter)."""
     import torch
     exporter = FrameExporter(output_dir, threads=export_threads, synchronous=sync_export) if writer else None
     done_steps, done_runs, t0 = 0, 0, time.perf_counter()
-    t_denoise = t_decode = 0.0
+    t_denoise = t_decode = t_measure = 0.0
+    lp = None
+    if writer and decode and metrics_dir is not None:
+        from .lpips import LpipsAlex
+        from .metrics import measure_video
+        lp = LpipsAlex.from_local_or_random().cuda()
+        Path(metrics_dir).mkdir(parents=True, exist_ok=True)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     for run in my_runs:
         if is_done(run, output_dir):
@@ -289,6 +295,16 @@ def run_worker(pipe, my_runs: Sequence[ExperimentConfig], output_dir: Path, writ
         ev[2].record()
         if writer:
             exporter.submit(frames, run)
+        if lp is not None and frames is not None:
+            # the reference's experiments/06 on the frames while they are still on the device (row f4)
+            tm = time.perf_counter()
+            m = measure_video(frames, lpips_fn=lp)
+            rec = {"video_name": run.video_name, "experiment_id": run.experiment_id, "num_frames": m.pop("num_frames"),
+                   "guidance_scale": run.guidance_scale, "num_inference_steps": run.num_inference_steps,
+                   "phase": run.phase, **m}
+            with open(Path(metrics_dir) / f"{run.experiment_id}_metrics.json", "w", encoding="utf-8") as f:
+                json.dump(rec, f, indent=2)
+            t_measure += time.perf_counter() - tm
         ev[2].synchronize()
         t_denoise += ev[0].elapsed_time(ev[1]) * 1e-3
         t_decode += ev[1].elapsed_time(ev[2]) * 1e-3
@@ -299,7 +315,7 @@ def run_worker(pipe, my_runs: Sequence[ExperimentConfig], output_dir: Path, writ
     if exporter is not None:
         exporter.finish()
     return {"runs": done_runs, "steps": done_steps, "seconds": time.perf_counter() - t0, "generate_seconds": t_gen,
-            "denoise_seconds": t_denoise, "decode_seconds": t_decode,
+            "denoise_seconds": t_denoise, "decode_seconds": t_decode, "measure_seconds": t_measure,
             "export_encode_seconds": 0.0 if exporter is None else exporter.encode_seconds,
             "export_stall_seconds": 0.0 if exporter is None else exporter.stall_seconds}
 
@@ -319,6 +335,8 @@ def main(argv=None) -> int:
     ap.add_argument("--limit", type=int, default=0, help="only the first LIMIT runs (smoke runs)")
     ap.add_argument("--sync-export", action="store_true",
                     help="encode PNG/GIF synchronously between videos, as the reference does (05:172-190)")
+    ap.add_argument("--measure", default=None, metavar="DIR",
+                    help="also write the reference's experiments/06 metrics (<id>_metrics.json) for every video into DIR")
     ap.add_argument("--export-threads", type=int, default=0,
                     help="encoder threads per writer rank (0: host cores / ranks on this node, at least 3)")
     ap.add_argument("--height", type=int, default=HEIGHT)
@@ -368,9 +386,10 @@ def main(argv=None) -> int:
     try:
         stats = run_worker(pipe, mine, out_dir, writer=(rank % per == 0), decode=not a.latent_only,
                            log=lambda m: print(f"[worker {worker}] {m}", flush=True), sync_export=a.sync_export,
-                           export_threads=a.export_threads)
+                           export_threads=a.export_threads, metrics_dir=Path(a.measure) if a.measure else None)
         is_w = rank % per == 0
-        keys = ("steps", "runs", "denoise_seconds", "decode_seconds", "export_encode_seconds", "export_stall_seconds")
+        keys = ("steps", "runs", "denoise_seconds", "decode_seconds", "measure_seconds", "export_encode_seconds",
+                "export_stall_seconds")
         t = torch.tensor([stats["seconds"]] + [float(stats[k]) if is_w else 0.0 for k in keys], device="cuda",
                          dtype=torch.float64)
         if world > 1:
