@@ -430,19 +430,6 @@ class AnimateDiffTransformer3D(_Packable):
         return _leaf.add(get_ops(_mode_of(self)), x, residual)
 
 
-# ----------------------------------------------------------------------------- layout helpers (module mode)
-def _to_rows(x_nchw: torch.Tensor) -> torch.Tensor:
-    """[N, C, h, w] (any float dtype) -> fp32 channels-last rows [N*h*w, C] on the GPU (view plumbing only)."""
-    if not x_nchw.is_cuda:
-        raise RuntimeError("b200ad modules need CUDA tensors (no CPU fallback exists)")
-    n, c, h, w = x_nchw.shape
-    return x_nchw.float().permute(0, 2, 3, 1).reshape(n * h * w, c).contiguous()
-
-
-def _from_rows(x: torch.Tensor, n: int, h: int, w: int, dtype) -> torch.Tensor:
-    return x.view(n, h, w, -1).permute(0, 3, 1, 2).to(dtype)
-
-
 def _mode_of(m: nn.Module) -> str:
     return getattr(m, "_b200_mode", "bf16")
 
@@ -511,13 +498,6 @@ class ResnetBlock2D(_Packable):
         h = self.conv2(self.dropout(self.nonlinearity(self.norm2(h))))
         x = input_tensor if self.conv_shortcut is None else self.conv_shortcut(input_tensor)
         return _leaf.add(o, x, h)
-
-
-def _rows_linear_f32(o: Ops, temb, lin: nn.Linear):
-    """time_emb_proj for more than 8 distinct embedding rows (module mode only): 8 rows per launch."""
-    t = temb.float().contiguous()
-    w, b = _dev_f(lin.weight), _dev_f(lin.bias)
-    return torch.cat([o.small_linear(t[i:i + 8].contiguous(), w, b, silu_in=True) for i in range(0, t.shape[0], 8)], 0)
 
 
 class Downsample2D(_Packable):
