@@ -209,6 +209,19 @@ int b200ad_video_warp_error(const unsigned char* frames_fhwc, int F, int H, int 
                             double* workspace, double* out, void* stream);
 int b200ad_video_gray_u8(const unsigned char* frames_fhwc, long long npix, int C, unsigned char* gray, void* stream);
 
+/* b200ad_video_pair_sums without a workspace argument and without any allocation.  No counterpart in the reference:
+ * added for callers that cannot call cudaMalloc (CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same inputs, `out` and results as b200ad_video_pair_sums; the per-block
+ * partial sums live in a file-scope `static __device__ __align__(256)` array of the library (149 184 bytes on every
+ * GPU that loads it, until exit), whose device address is taken once per device with cudaGetSymbolAddress.
+ * Limit: F <= b200ad_static_max_frames() = 64; larger F returns -1 with b200ad_last_error() naming the limit.
+ * Calls no cudaMalloc / cudaFree / allocating library routine.  Every call on a device shares the array (it keeps the
+ * last call's partials; each call overwrites all it reads, so nothing needs clearing): calls that overlap on the GPU
+ * (different streams, no ordering between them) race -- serialise them. */
+int b200ad_static_max_frames(void);
+int b200ad_video_pair_sums_static(const unsigned char* frames_fhwc, int F, long long n_per_frame, double* out,
+                                  void* stream);
+
 /* LPIPS (AlexNet) between consecutive frames (replaces lpips.LPIPS(net='alex') at 06:101-131): lpips_input applies the
  * [0,255] -> [-1,1] map and LPIPS' ScalingLayer; conv2d_direct is an fp32 direct convolution over NHWC (weights
  * [cout, kh, kw, cin], any kernel / stride / padding, bias, optional ReLU: AlexNet's 11x11 s4, 5x5 and 3x3 layers);

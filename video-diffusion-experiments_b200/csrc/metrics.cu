@@ -381,3 +381,63 @@ extern "C" int b200ad_lpips_layer(const float* feat_nhwc, int N, int hw, int C, 
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ----------------------------------------------------------------------------- no-allocation variant
+// b200ad_video_pair_sums_static: b200ad_video_pair_sums for callers that cannot allocate (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  The per-block partial sums live in a file-scope device array
+// instead of a caller-provided workspace; nothing is allocated, by this library or by any library it calls.
+//   * limit: F <= B200AD_STATIC_MAX_FRAMES (64) frames -> 148 blocks * 2 sums * 63 pairs doubles = 149 184 bytes,
+//     held by every GPU that loads the library until the process exits;
+//   * in host code `g_pair_scratch` is only a host-side stand-in for the array, NOT a device address: the address is
+//     taken once per device, with that device current, by cudaGetSymbolAddress, and that pointer goes to the kernels;
+//   * all calls on a device share the array.  pair_sums_kernel writes every partial that reduce_rows_kernel reads
+//     (each block stores its two sums unconditionally), so nothing has to start at zero and nothing is cleared; the
+//     array keeps the last call's partials.  Two calls that overlap on the GPU (different streams without an ordering
+//     event) race on it -- serialise them.
+static constexpr int kStaticMaxFrames = 64;
+static constexpr int kStaticBlocks = 148;          // == b200ad_metric_blocks()
+static __device__ __align__(256) double g_pair_scratch[kStaticBlocks * 2 * (kStaticMaxFrames - 1)];
+
+static constexpr int kMaxDevices = 64;
+static double* g_pair_scratch_ptr[kMaxDevices];    // per device, filled on first use (0 = not yet)
+
+static int pair_scratch_for_current_device(double** ptr) {
+  int dev = -1;
+  B200AD_CHECK_CUDA(cudaGetDevice(&dev));
+  B200AD_REQUIRE(dev >= 0 && dev < kMaxDevices, "video_pair_sums_static: device ordinal %d is beyond %d", dev, kMaxDevices);
+  double* p = __atomic_load_n(&g_pair_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    // the array's device address ON THE CURRENT DEVICE (each device that loads the module has its own copy)
+    B200AD_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, g_pair_scratch));
+    B200AD_REQUIRE(p != nullptr, "video_pair_sums_static: cudaGetSymbolAddress returned a null pointer");
+    __atomic_store_n(&g_pair_scratch_ptr[dev], p, __ATOMIC_RELEASE);   // same value from every thread: benign if raced
+  }
+  *ptr = p;
+  return 0;
+}
+
+extern "C" int b200ad_static_max_frames(void) { return kStaticMaxFrames; }
+
+extern "C" int b200ad_video_pair_sums_static(const unsigned char* frames_fhwc, int F, long long n_per_frame, double* out,
+                                             void* stream) {
+  static_assert(kStaticBlocks == 148, "keep in step with b200ad_metric_blocks()");
+  B200AD_REQUIRE(frames_fhwc && out && F >= 2 && n_per_frame > 0, "video_pair_sums_static: bad arguments");
+  B200AD_REQUIRE(F <= kStaticMaxFrames,
+                 "video_pair_sums_static: F = %d frames is beyond the static scratch limit of %d frames; use "
+                 "b200ad_video_pair_sums with a caller-provided workspace", F, kStaticMaxFrames);
+  B200AD_REQUIRE(((uintptr_t)frames_fhwc & 15) == 0 && n_per_frame % 16 == 0,
+                 "video_pair_sums_static: frames must be 16-byte aligned with a multiple of 16 bytes per frame");
+  B200AD_REQUIRE(b200ad_metric_blocks() == kStaticBlocks, "video_pair_sums_static: block count changed");
+  double* scratch = nullptr;
+  const int rc = pair_scratch_for_current_device(&scratch);
+  if (rc != 0) return rc;
+  const int nb = kStaticBlocks;
+  B200AD_CHECK_CUDA(pdl_launch(pair_sums_kernel, dim3(nb, F - 1), dim3(MT), (size_t)0, (cudaStream_t)stream,
+                               (const uint8_t*)frames_fhwc, F, n_per_frame, scratch));
+  const int rows = 2 * (F - 1);
+  B200AD_CHECK_CUDA(pdl_launch(reduce_rows_kernel, dim3((rows * 32 + 127) / 128), dim3(128), (size_t)0,
+                               (cudaStream_t)stream, (const double*)scratch, rows, nb, out));
+  count_launch(2);
+  B200AD_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

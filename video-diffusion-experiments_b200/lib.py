@@ -52,6 +52,8 @@ SIGNATURES = {
     "b200ad_video_to_u8": [_P, _I, _I, _I, _I, _P, _P],
     "b200ad_metric_blocks": [],
     "b200ad_video_pair_sums": [_P, _I, _L, _P, _P, _P],
+    "b200ad_static_max_frames": [],
+    "b200ad_video_pair_sums_static": [_P, _I, _L, _P, _P],
     "b200ad_video_warp_error": [_P, _I, _I, _I, _I, _P, _P, _P, _P],
     "b200ad_video_gray_u8": [_P, _L, _I, _P, _P],
     "b200ad_lpips_input": [_P, _L, _P, _P],
