@@ -35,6 +35,23 @@ if which in ("all", "big"):
     for n, cin, cout, r in [(32, 320, 320, 64), (32, 1280, 1280, 16)]:
         src, w = bf(n * r * r, cin), bf(cout, 9 * cin, scale=(9 * cin) ** -0.5)
         run(f"conv {cin}->{cout}@{r}", lambda: o.conv3x3(src, w, n, r, r))
+if which in ("small",):
+    # the deepest level (M = 2048 rows, one tile per cluster) and level 2 (M = 8192)
+    for (M, N, K, kind) in [(2048, 1280, 1280, "res32"), (2048, 1280, 5120, "res32"), (2048, 3840, 1280, "op"),
+                            (2048, 10240, 1280, "geglu"), (8192, 1280, 1280, "res32"), (8192, 1280, 5120, "res32")]:
+        a, w = bf(M, K), bf(N, K, scale=K ** -0.5)
+        bias = torch.randn(N, device="cuda")
+        if kind == "op":
+            out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+            fn = lambda: o.gemm(a, w, bias=bias, out_op=out)
+        elif kind == "res32":
+            res = torch.randn(M, N, device="cuda")
+            fn = lambda: o.gemm(a, w, bias=bias, residual=res, out_f32=res)
+        else:
+            out = torch.empty(M, N // 2, device="cuda", dtype=torch.bfloat16)
+            fn = lambda: o.gemm(a, w, bias=bias, out_op=out, geglu=True)
+        run(f"gemm {M}x{N}x{K} {kind} ({2.0 * M * N * K / 1e9:.1f} GFLOP)", fn)
+    sys.exit(0)
 # the level-0 (M = 131072 rows) GEMMs of the step: HBM-bound by the fp32 residual stream
 for (M, N, K, kind) in [(131072, 320, 320, "op"), (131072, 320, 320, "res32"), (131072, 960, 320, "op"),
                         (131072, 320, 1280, "res32"), (131072, 2560, 320, "geglu"), (32768, 640, 640, "res32"),

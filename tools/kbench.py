@@ -74,7 +74,7 @@ def gemm():
     for hw, C in [(4096, 320), (1024, 640), (256, 1280), (64, 1280)]:
         M = 32 * hw
         shapes += [(M, C, C, "res32"), (M, 3 * C, C, "op"), (M, 8 * C, C, "geglu"), (M, C, 4 * C, "res32"),
-                   (M, C, 4 * C, "resop")]
+                   (M, C, 4 * C, "resop"), (M, C, 5 * C, "res32")]     # K = 5C: the folded FF2 + proj_out GEMM
     for M, N, K, kind in shapes:
         a, w = bf(M, K), bf(N, K, scale=K ** -0.5)
         bias = torch.randn(N, device="cuda")

@@ -18,6 +18,7 @@ is a kernel of libb200ad.so (ops.py); torch is used for allocation and views onl
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
@@ -26,7 +27,7 @@ import torch.nn as nn
 
 from . import leaf as _leaf
 from .leaf import Conv2d, GroupNorm, LayerNorm, Linear, SiLU
-from .ops import Ops, get_ops
+from .ops import Ops, _empty, get_ops
 
 
 @dataclass
@@ -185,7 +186,8 @@ class Attention(_Packable):
         o.gemm(att, p["wo"], bias=p["bo"], residual=h, out_f32=h)
         return h
 
-    def run_cross(self, st: _State, n_op, h, nimg: int, L: int):
+    def run_cross(self, st: _State, n_op, h, nimg: int, L: int, h_op=None):
+        """h_op (optional, operand-typed [rows, C] view): also receives the updated stream (see _fold_tail)."""
         o = st.o
         p = self.packed_cross(o)
         H, C, dp = self.heads, self.query_dim, p["dp"]
@@ -198,15 +200,15 @@ class Attention(_Packable):
         _, q = o.gemm(n_op, p["wq"], want_op=True)
         Lk = st.ctx_rows // (nimg // st.kv_div)
         att = o.attention(q, kv[:, :hd], kv[:, hd:], nimg, H, L, Lk, C // H, dp, st.kv_div)
-        o.gemm(att, p["wo"], bias=p["bo"], residual=h, out_f32=h)
+        o.gemm(att, p["wo"], bias=p["bo"], residual=h, out_f32=h, out_op=h_op)
         return h
 
-    def run_temporal(self, st: _State, n_op, h, hw: int):
+    def run_temporal(self, st: _State, n_op, h, hw: int, h_op=None):
         o = st.o
         p = self.packed_temporal(o)
         _, qkv = o.gemm(n_op, p["wqkv_t"], want_op=True)
         att = o.temporal_attention(qkv, st.B, st.F, hw, self.query_dim, self.heads)
-        o.gemm(att, p["wo"], bias=p["bo"], residual=h, out_f32=h)
+        o.gemm(att, p["wo"], bias=p["bo"], residual=h, out_f32=h, out_op=h_op)
         return h
 
     def forward(self, hidden_states, encoder_hidden_states=None, attention_mask=None, **kw):
@@ -251,9 +253,14 @@ class FeedForward(_Packable):
             hidden_states = m(hidden_states)
         return hidden_states
 
-    def run(self, st: _State, n_op, h, *, op_only: bool):
-        """h + ff(n): returns fp32 (in place) or, when the caller only needs an operand, the operand-typed sum."""
+    def run(self, st: _State, n_op, h, *, op_only: bool, gate_out=None):
+        """h + ff(n): returns fp32 (in place) or, when the caller only needs an operand, the operand-typed sum.
+        gate_out (operand-typed [rows, 4C] view): only the GEGLU half runs, written there; the second Linear is
+        folded into the parent's proj_out GEMM (_fold_tail)."""
         o, p = st.o, self.packed(st.o)
+        if gate_out is not None:
+            o.gemm(n_op, p["w1"], bias=p["b1"], out_op=gate_out, geglu=True)
+            return None
         _, g = o.gemm(n_op, p["w1"], bias=p["b1"], want_op=True, geglu=True)
         if op_only:
             return o.gemm(g, p["w2"], bias=p["b2"], residual=h, want_op=True)[1]
@@ -318,23 +325,46 @@ class BasicTransformerBlock(_Packable):
                                        attention_mask=encoder_attention_mask))
         return _leaf.add(o, x, self.ff(self.norm3(x)))
 
-    def run(self, st: _State, h, nimg: int, hw: int, last: bool = True):
+    def run(self, st: _State, h, nimg: int, hw: int, last: bool = True, fold: bool = False):
         """h: fp32 [nimg*hw, C] residual stream (updated in place).  last=True: returns the operand-typed block
         output (its only consumer is the proj_out GEMM) and leaves h WITHOUT the feed-forward term; last=False
-        (another block follows): h += ff and h is returned."""
+        (another block follows): h += ff and h is returned.  last and fold: returns the operand matrix
+        [rows, 5C] = (h after attn2 | GEGLU gate) for the parent's folded proj_out GEMM (_fold_tail)."""
         o, p = st.o, self.packed(st.o)
+        C = h.shape[1]
+        cat = _empty((h.shape[0], 5 * C), h.device, o.op_dtype) if (last and fold) else None
+        h_op = None if cat is None else cat[:, :C]
         if self.temporal:
             n = o.layer_norm(h, p["g1"], p["b1"], self.norm1.eps, pe=p["pe"], hw=hw, frames=st.F)
             self.attn1.run_temporal(st, n, h, hw)
             n = o.layer_norm(h, p["g2"], p["b2"], self.norm2.eps, pe=p["pe"], hw=hw, frames=st.F)
-            self.attn2.run_temporal(st, n, h, hw)
+            self.attn2.run_temporal(st, n, h, hw, h_op=h_op)
         else:
             n = o.layer_norm(h, p["g1"], p["b1"], self.norm1.eps)
             self.attn1.run_spatial_self(st, n, h, nimg, hw)
             n = o.layer_norm(h, p["g2"], p["b2"], self.norm2.eps)
-            self.attn2.run_cross(st, n, h, nimg, hw)
+            self.attn2.run_cross(st, n, h, nimg, hw, h_op=h_op)
         n = o.layer_norm(h, p["g3"], p["b3"], self.norm3.eps)
+        if cat is not None:
+            self.ff.run(st, n, h, op_only=True, gate_out=cat[:, C:])
+            return cat
         return self.ff.run(st, n, h, op_only=last)
+
+
+def _fold_tail(o: Ops, ff: "FeedForward", w_out: torch.Tensor, b_out: torch.Tensor):
+    """The last block's second feed-forward Linear and the transformer's proj_out are two linear maps with nothing
+    but the residual add between them:
+        x + Wout (h + W2 g + b2) + bout  =  x + [h | g] [Wout | Wout W2]^T + (Wout b2 + bout)
+    so they run as ONE GEMM with K = 5C over the operand matrix (h | g) that attn2's out-projection (operand copy of
+    the stream) and the GEGLU GEMM write side by side.  Saves the 4 B/element re-read of the fp32 stream, the
+    2 B/element write + read of the block output and one launch per transformer.  The composite is formed in fp64 and
+    rounded to the operand type once.  bf16 kernel mode only (the fp32 validation mode keeps the module's algebra);
+    B200AD_FOLD_TAIL=0 turns it off."""
+    if o.mode != "bf16" or os.environ.get("B200AD_FOLD_TAIL", "1") == "0":
+        return None, None
+    w2, b2 = ff.net[2].weight.detach().double(), ff.net[2].bias.detach().double()
+    wo, bo = w_out.detach().double().reshape(w_out.shape[0], -1), b_out.detach().double()
+    return _dev_w(o, torch.cat([wo, wo @ w2], 1)), _dev_f(wo @ b2 + bo)
 
 
 class Transformer2DModel(_Packable):
@@ -350,9 +380,11 @@ class Transformer2DModel(_Packable):
 
     def _pack(self, o: Ops):
         c = self.proj_in.weight.shape[0]
+        wcat, bcat = _fold_tail(o, self.transformer_blocks[-1].ff, self.proj_out.weight, self.proj_out.bias)
         return {"gn_g": _dev_f(self.norm.weight), "gn_b": _dev_f(self.norm.bias),
                 "win": _dev_w(o, self.proj_in.weight.reshape(c, c)), "bin": _dev_f(self.proj_in.bias),
-                "wout": _dev_w(o, self.proj_out.weight.reshape(c, c)), "bout": _dev_f(self.proj_out.bias)}
+                "wout": _dev_w(o, self.proj_out.weight.reshape(c, c)), "bout": _dev_f(self.proj_out.bias),
+                "wcat": wcat, "bcat": bcat}
 
     def forward(self, hidden_states, encoder_hidden_states=None, timestep=None, added_cond_kwargs=None,
                 class_labels=None, cross_attention_kwargs=None, attention_mask=None, encoder_attention_mask=None,
@@ -376,6 +408,10 @@ class Transformer2DModel(_Packable):
         h, _ = o.gemm(a, p["win"], bias=p["bin"], want_f32=True)
         for blk in self.transformer_blocks[:-1]:
             blk.run(st, h, nimg, hw, last=False)
+        if p["wcat"] is not None:
+            cat = self.transformer_blocks[-1].run(st, h, nimg, hw, fold=True)
+            o.gemm(cat, p["wcat"], bias=p["bcat"], residual=x, out_f32=x, stats_hw=hw)
+            return x
         hb = self.transformer_blocks[-1].run(st, h, nimg, hw)
         o.gemm(hb, p["wout"], bias=p["bout"], residual=x, out_f32=x, stats_hw=hw)     # x feeds a GroupNorm next
         return x
@@ -395,9 +431,11 @@ class AnimateDiffTransformer3D(_Packable):
         self.proj_out = Linear(channels, channels)
 
     def _pack(self, o: Ops):
+        wcat, bcat = _fold_tail(o, self.transformer_blocks[-1].ff, self.proj_out.weight, self.proj_out.bias)
         return {"gn_g": _dev_f(self.norm.weight), "gn_b": _dev_f(self.norm.bias),
                 "win": _dev_w(o, self.proj_in.weight), "bin": _dev_f(self.proj_in.bias),
-                "wout": _dev_w(o, self.proj_out.weight), "bout": _dev_f(self.proj_out.bias)}
+                "wout": _dev_w(o, self.proj_out.weight), "bout": _dev_f(self.proj_out.bias),
+                "wcat": wcat, "bcat": bcat}
 
     def run(self, st: _State, x, hw: int):
         o, p = st.o, self.packed(st.o)
@@ -407,6 +445,10 @@ class AnimateDiffTransformer3D(_Packable):
         h, _ = o.gemm(a, p["win"], bias=p["bin"], want_f32=True)
         for blk in self.transformer_blocks[:-1]:
             blk.run(st, h, nimg, hw, last=False)
+        if p["wcat"] is not None:
+            cat = self.transformer_blocks[-1].run(st, h, nimg, hw, fold=True)
+            o.gemm(cat, p["wcat"], bias=p["bcat"], residual=x, out_f32=x, stats_hw=hw)
+            return x
         hb = self.transformer_blocks[-1].run(st, h, nimg, hw)
         o.gemm(hb, p["wout"], bias=p["bout"], residual=x, out_f32=x, stats_hw=hw)     # x feeds a GroupNorm next
         return x
