@@ -93,6 +93,17 @@ int b200ad_conv3x3_stats(int op_dtype, const void* src, const void* W, int nimg,
                          int mode, const float* bias, const float* row_bias, int rb_div, int ld_rb,
                          const float* residual, long long ld_res, float* out_f32, long long ld_o32, float* col_stats,
                          void* stream);
+
+/* Upsample2D = F.interpolate(scale_factor=2, mode="nearest") + Conv2d(C, C, 3, padding=1) of the UNet's up blocks and the
+ * VAE decoder WITHOUT the upsampled image: four 2x2 convolutions over the low-resolution
+ * source, one per output phase (py, px).  src: operand-typed NHWC [nimg, h, w, cin]; outputs are rows of the
+ * [nimg, 2h, 2w] image.  W4: [4 phases (py*2+px)][cout][2x2 taps (ty*2+tx)][cin] where tap (ty, tx) of phase (py, px) is
+ * the sum of the 3x3 weights w[ky][kx] with floor((py + ky - 1) / 2) == ty - 1 + py (same in x), reading source pixel
+ * (y + ty - 1 + py, x + tx - 1 + px).  bf16 (tcgen05) path only.  col_stats (optional, fp32-only output): as
+ * b200ad_conv3x3_stats, 4 * b200ad_stats_slots(1, h, w) slots per image. */
+int b200ad_upconv3x3(int op_dtype, const void* src, const void* W4, int nimg, int h, int w, int cin, int cout,
+                     const float* bias, float* out_f32, long long ld_o32, void* out_op, long long ld_oop,
+                     float* col_stats, void* stream);
 int b200ad_gn_apply_stats(int op_dtype, const float* x0, int c0, const float* st0, int spi0, const float* x1, int c1,
                           const float* st1, int spi1, int nimg, int hw, int groups, int frames_per_stat, float eps,
                           const float* gamma, const float* beta, int silu, float* meanrstd_ws, void* out_op,

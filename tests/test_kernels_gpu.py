@@ -170,6 +170,49 @@ def test_group_norm_is_deterministic_across_launches(mode, c0, c1):
     assert bad == 0, f"{bad} of 300 launches differ from the first"
 
 
+@pytest.mark.parametrize("n,h,w,cin,cout,exact", [(2, 32, 32, 64, 64, True), (3, 8, 8, 128, 320, True),
+                                                  (5, 16, 16, 64, 128, False), (2, 12, 20, 64, 64, False),
+                                                  (1, 64, 64, 64, 320, False), (4, 8, 8, 320, 64, True)])
+def test_upconv3x3_subpixel_matches_upsample_then_conv(n, h, w, cin, cout, exact):
+    """b200ad_upconv3x3 (nearest x2 + conv3x3 as four 2x2 sub-pixel convolutions over the low-resolution image) against
+    F.interpolate(nearest) + conv2d in fp32.  exact=True: weights are multiples of 1/64 in [-1/2, 1/2], so the summed
+    sub-pixel taps are bf16-exact and only the accumulation order differs (2e-5); otherwise the summed taps are rounded
+    to bf16 once more than the direct form's weights (4e-3).  Also: the GroupNorm column statistics of the four phase
+    launches cover the whole output image, and the GroupNorm that consumes them needs no statistics pass."""
+    from b200ad.unet import _pack_upconv3x3
+    o = ops("bf16")
+    x = bf(rnd(n, h, w, cin, seed=1))
+    if exact:
+        g = torch.Generator().manual_seed(2)
+        wt = torch.randint(-32, 33, (cout, cin, 3, 3), generator=g).float() / 64.0
+    else:
+        wt = bf(rnd(cout, cin, 3, 3, seed=2, scale=(9 * cin) ** -0.5))
+    b = rnd(cout, seed=3) + 0.3
+    up = F.interpolate(x.permute(0, 3, 1, 2), scale_factor=2.0, mode="nearest").permute(0, 2, 3, 1).contiguous()
+    ref = _conv_ref(up, wt, b).reshape(n * 4 * h * w, cout)
+    w4 = _pack_upconv3x3(o, wt)
+    assert w4.shape == (4, cout, 4 * cin)
+    n0 = lib_launches()
+    out = o.upconv3x3(x.to(DEV, o.op_dtype), w4, n, h, w, bias=b.to(DEV), stats=True)
+    assert lib_launches() - n0 == 4
+    assert rel(out.cpu(), ref) < (2e-5 if exact else 4e-3)
+    supported = o._stats_ok(True, h, w) > 0
+    assert (out.data_ptr() in o.colstats) == supported
+    gamma, beta = rnd(cout, seed=5), rnd(cout, seed=6)
+    gref = F.silu(F.group_norm(out.cpu().view(n, 4 * h * w, cout).permute(0, 2, 1), 32, gamma, beta, eps=1e-5)
+                  .permute(0, 2, 1).reshape(n * 4 * h * w, cout))
+    n0 = lib_launches()
+    gn = o.group_norm(out, None, n, 4 * h * w, 32, gamma.to(DEV), beta.to(DEV), 1e-5, silu=True)
+    if supported:
+        assert lib_launches() - n0 == 2                                  # finalize + apply
+        st, spi = o.colstats[out.data_ptr()][:2]
+        tot = st.view(n, spi, cout, 2).sum(1).cpu()
+        per_img = out.cpu().view(n, 4 * h * w, cout)
+        assert (tot[..., 0] - per_img.sum(1)).abs().max() < 2e-3 * (4 * h * w) ** 0.5
+        assert rel(tot[..., 1], (per_img ** 2).sum(1)) < 1e-5
+    assert rel(gn.cpu(), gref) < 4e-3
+
+
 @pytest.mark.parametrize("nimg,h,w,cin,cout,fps", [(4, 16, 16, 64, 320, 1), (6, 8, 8, 64, 128, 1), (8, 8, 8, 128, 320, 4),
                                                    (3, 12, 12, 64, 64, 1), (2, 24, 40, 64, 128, 1), (4, 32, 32, 64, 640, 2),
                                                    (5, 8, 8, 64, 64, 1), (2, 64, 64, 64, 320, 1)])

@@ -189,4 +189,46 @@ int b200ad_conv3x3_stats(int op_dtype, const void* src, const void* W, int nimg,
                    out_f32, ld_o32, nullptr, 0, col_stats, stream);
 }
 
+// nearest-x2 upsample followed by conv3x3 (pad 1) as four 2x2 convolutions over the LOW-resolution image, one per output
+// phase (py, px): output pixel (2y+py, 2x+px) reads the upsampled pixels (2y+py+dy, 2x+px+dx), dy, dx in {-1,0,1}, i.e.
+// the source pixels y + floor((py+dy)/2): rows {y-1, y} for py = 0 and {y, y+1} for py = 1 (columns alike), with the
+// 3x3 weights that land on the same source pixel summed beforehand by the caller.  4/9 of the MACs of the direct form
+// and the 4x larger upsampled image is never written.  Zero padding agrees: an upsampled pixel outside the image is a
+// source pixel outside the image, which the TMA load zero-fills.
+int b200ad_upconv3x3(int op_dtype, const void* src, const void* W4, int nimg, int h, int w, int cin, int cout,
+                     const float* bias, float* out_f32, long long ld_o32, void* out_op, long long ld_oop,
+                     float* col_stats, void* stream) {
+  B200AD_REQUIRE(src && W4, "upconv3x3: null operand");
+  B200AD_REQUIRE(out_f32 || out_op, "upconv3x3: no output buffer");
+  B200AD_REQUIRE(op_dtype == 0, "upconv3x3: tcgen05 (bf16 operand) path only");
+  B200AD_REQUIRE(!col_stats || (out_f32 && !out_op), "upconv3x3: column statistics need an fp32-only output");
+  int nb, hb, wb;
+  conv_box(h, w, &nb, &hb, &wb);
+  const int tiles_per_img = ((w + wb - 1) / wb) * ((h + hb - 1) / hb);
+  for (int ph = 0; ph < 4; ++ph) {
+    const int py = ph >> 1, px = ph & 1;
+    GemmArgs a;
+    memset(&a, 0, sizeof(a));
+    a.A = src;
+    a.W = reinterpret_cast<const char*>(W4) + (size_t)ph * cout * 4 * cin * 2;
+    a.M = nimg * h * w; a.N = cout; a.K = 4 * cin;
+    ConvGeom& g = a.conv;
+    g.enabled = 1;
+    g.nimg = nimg; g.h = h; g.w = w; g.cin = cin; g.ntaps = 4;
+    g.src_h = h; g.src_w = w; g.src_nimg = nimg;
+    for (int ty = 0; ty < 2; ++ty)
+      for (int tx = 0; tx < 2; ++tx) {
+        const int t = ty * 2 + tx;
+        g.tap_dy[t] = ty - 1 + py; g.tap_dx[t] = tx - 1 + px; g.tap_dn[t] = 0;
+      }
+    g.n_box = nb; g.h_box = hb; g.w_box = wb;
+    g.out_scale = 2; g.out_py = py; g.out_px = px;
+    g.stats_slots = 4 * tiles_per_img; g.stats_slot0 = ph * tiles_per_img;
+    fill_epilogue(a.epi, bias, nullptr, 1, 0, nullptr, 0, out_f32, ld_o32, out_op, ld_oop, 0);
+    a.epi.col_stats = col_stats;
+    if (int rc = gemm_bf16_tc(a, (cudaStream_t)stream)) return rc;
+  }
+  return 0;
+}
+
 }  // extern "C"

@@ -15,6 +15,12 @@ struct ConvGeom {
   int tap_dn[9];               // ... of source image index n + dn (phase-split stride-2 input stacks 4 phases on n)
   int src_nimg, src_h, src_w;  // source tensor geometry [src_nimg, src_h, src_w, cin]
   int n_box, h_box, w_box;     // tcgen05 path: M tile (128 rows) = n_box*h_box*w_box output pixels
+  // Sub-pixel output (nearest-x2 upsample + conv3x3 as four 2x2 convolutions, one per output phase): pixel (n, y, x) of
+  // this launch is pixel (n, out_scale*y + out_py, out_scale*x + out_px) of an [nimg, out_scale*h, out_scale*w] image.
+  // out_scale = 0 or 1: plain output.  Applies to out_f32 / out_op / residual alike (tcgen05 path only).
+  int out_scale, out_py, out_px;
+  // column statistics: slots per image of the whole output (0: the tiles of this launch) and this launch's first slot
+  int stats_slots, stats_slot0;
 };
 
 struct Epilogue {

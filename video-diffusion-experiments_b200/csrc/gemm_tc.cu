@@ -65,6 +65,7 @@ struct TcParams {
   float2* stats;
   int stats_spi;               // statistic slots per image
   int stats_mq;                // 32-row quarters of a tile merged into one slot (4: the whole tile lies in one image)
+  int stats_slot0;             // conv: first slot of this launch inside an image's stats_spi slots (sub-pixel phases)
   int off_stat;                // smem: [2 groups][MAX_NBUF][4 quarters][32 columns] float2 hand-over to the I/O warp
 };
 
@@ -468,7 +469,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (j * st_mq >= 4) continue;
           if (p.conv) {
             const int img = t.n0 + j;
-            if (img < p.nimg) st_off[j] = ((long long)img * p.stats_spi + (t.m_tile % (p.tiles_x * p.tiles_y))) * p.N;
+            if (img < p.nimg) st_off[j] = ((long long)img * p.stats_spi + p.stats_slot0 + (t.m_tile % (p.tiles_x * p.tiles_y))) * p.N;
           } else {
             const long long row0 = (long long)t.m_tile * BM + j * 32 * st_mq;
             if (row0 < p.M) st_off[j] = (row0 / (32 * st_mq)) * p.N;
@@ -743,10 +744,14 @@ static int make_out_map(CUtensorMap* tm, const void* ptr, long long ld, int ncol
   const CUtensorMapDataType dt = elem == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   const CUtensorMapSwizzle sw = elem == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   if (g.enabled) {
+    // sub-pixel phase (out_scale = 2): the launch's pixels are every 2nd pixel of every 2nd row of the full image
+    const uint64_t sc = g.out_scale > 1 ? (uint64_t)g.out_scale : 1u;
+    const uint64_t wf = sc * g.w, hf = sc * g.h;
+    const char* base = reinterpret_cast<const char*>(ptr) + ((uint64_t)g.out_py * wf + (uint64_t)g.out_px) * ld * elem;
     uint64_t dims[4] = {(uint64_t)ncols, (uint64_t)g.w, (uint64_t)g.h, (uint64_t)g.nimg};
-    uint64_t str[3] = {(uint64_t)ld * elem, (uint64_t)g.w * ld * elem, (uint64_t)g.h * g.w * ld * elem};
+    uint64_t str[3] = {sc * ld * elem, sc * wf * ld * elem, hf * wf * ld * elem};
     uint32_t box[4] = {32u, (uint32_t)g.w_box, (uint32_t)g.h_box, (uint32_t)g.n_box};
-    return make_tmap(tm, dt, ptr, 4, dims, str, box, sw);
+    return make_tmap(tm, dt, base, 4, dims, str, box, sw);
   }
   uint64_t dims[2] = {(uint64_t)ncols, (uint64_t)a.M};
   uint64_t str[1] = {(uint64_t)ld * elem};
@@ -792,6 +797,7 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
                    g.w_box, BM);
     B200AD_REQUIRE(a.K == g.ntaps * g.cin, "conv: K=%d != ntaps*cin=%d", a.K, g.ntaps * g.cin);
     B200AD_REQUIRE(a.M == g.nimg * g.h * g.w, "conv: M=%d != nimg*h*w", a.M);
+    B200AD_REQUIRE(g.out_scale <= 1 || !e.row_bias, "conv: a row bias cannot be combined with a sub-pixel output");
     p.conv = 1;
     p.nimg = g.nimg; p.h = g.h; p.w = g.w;
     p.n_box = g.n_box; p.h_box = g.h_box; p.w_box = g.w_box;
@@ -817,7 +823,10 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
       p.stats_mq = g.h_box * g.w_box / 32;                 // = 4 / n_box: quarters of one image inside a tile
       B200AD_REQUIRE(p.stats_mq >= 1, "conv: column statistics need >= 32 pixels of one image per tile (box %dx%dx%d)",
                      g.n_box, g.h_box, g.w_box);
-      p.stats_spi = p.tiles_x * p.tiles_y;
+      p.stats_spi = g.stats_slots > 0 ? g.stats_slots : p.tiles_x * p.tiles_y;
+      p.stats_slot0 = g.stats_slot0;
+      B200AD_REQUIRE(p.stats_slot0 >= 0 && p.stats_slot0 + p.tiles_x * p.tiles_y <= p.stats_spi,
+                     "conv: statistic slots %d + %d beyond %d", p.stats_slot0, p.tiles_x * p.tiles_y, p.stats_spi);
     } else {
       B200AD_REQUIRE(e.stats_hw > 0 && e.stats_hw % 32 == 0 && a.M % e.stats_hw == 0,
                      "gemm: column statistics need rows per image (%d) to be a multiple of 32 dividing M=%d", e.stats_hw, a.M);

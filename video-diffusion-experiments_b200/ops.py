@@ -53,9 +53,9 @@ class KernelProfiler:
     def summary(self):
         torch.cuda.synchronize()
         fam = {}
-        for name, flops, nbytes, e0, e1 in self.records:
+        for name, flops, nbytes, e0, e1, launches in self.records:
             d = fam.setdefault(name, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
-            d["launches"] += 1
+            d["launches"] += launches
             d["ms"] += e0.elapsed_time(e1)
             d["flops"] += flops
             d["bytes"] += nbytes
@@ -67,10 +67,10 @@ class KernelProfiler:
 
 
 class _Rec:
-    __slots__ = ("prof", "name", "flops", "nbytes", "e0")
+    __slots__ = ("prof", "name", "flops", "nbytes", "e0", "launches")
 
-    def __init__(self, prof, name, flops, nbytes):
-        self.prof, self.name, self.flops, self.nbytes = prof, name, flops, nbytes
+    def __init__(self, prof, name, flops, nbytes, launches=1):
+        self.prof, self.name, self.flops, self.nbytes, self.launches = prof, name, flops, nbytes, launches
 
     def __enter__(self):
         if self.prof is not None:
@@ -81,7 +81,7 @@ class _Rec:
         if self.prof is not None:
             e1 = torch.cuda.Event(enable_timing=True)
             e1.record()
-            self.prof.records.append((self.name, self.flops, self.nbytes, self.e0, e1))
+            self.prof.records.append((self.name, self.flops, self.nbytes, self.e0, e1, self.launches))
         return False
 
 
@@ -93,8 +93,8 @@ class Ops:
     """Kernel front-end bound to one operand mode: 'bf16' (tcgen05 tensor cores) or 'fp32' (SIMT)."""
     profiler: Optional[KernelProfiler] = None       # class-level: set by bench.py around an eager pass
 
-    def _rec(self, name, flops=0.0, nbytes=0.0):
-        return _Rec(Ops.profiler, name, flops, nbytes)
+    def _rec(self, name, flops=0.0, nbytes=0.0, launches=1):
+        return _Rec(Ops.profiler, name, flops, nbytes, launches)
 
     # GroupNorm column statistics emitted by GEMM / conv epilogues: data_ptr of the fp32 output -> (stats, spi, nimg,
     # hw, C, out tensor).  A later writer of the same buffer without statistics drops the entry.
@@ -191,6 +191,28 @@ class Ops:
                 0 if residual is None else residual.stride(0), _ptr(out_f32), cout, _ptr(out_op), cout, _stream())
         _lib.check(rc, "b200ad_conv3x3")
         return out_f32, out_op
+
+    def upconv3x3(self, src, w4, nimg, h, wd, *, bias=None, stats=False):
+        """nearest-x2 upsample + 3x3 conv of the low-resolution NHWC `src` [nimg*h*wd, cin] (operand-typed) as four
+        2x2 sub-pixel convolutions (b200ad_upconv3x3); w4 [4, cout, 4*cin] from pack_upconv_weights().  Returns the
+        fp32 rows of the [nimg, 2h, 2wd] image.  bf16 mode only.  FLOPs booked are the executed ones (4/9 of the
+        direct form's)."""
+        _need_cuda(src, w4)
+        assert self.op == BF16, "upconv3x3 exists on the tcgen05 path only"
+        assert src.dtype == self.op_dtype and w4.dtype == self.op_dtype and src.is_contiguous() and w4.is_contiguous()
+        _, cout, k4 = w4.shape
+        cin = k4 // 4
+        M = nimg * 4 * h * wd
+        out = _empty((M, cout), src.device, torch.float32)
+        spi = self._stats_ok(True, h, wd) if stats else 0
+        st = _empty((nimg * 4 * spi, cout, 2), src.device, torch.float32) if spi else None
+        with self._rec("conv3x3", 2.0 * M * cout * k4, _nb(src, w4, out, st), launches=4):
+            rc = self.L.b200ad_upconv3x3(self.op, src.data_ptr(), w4.data_ptr(), nimg, h, wd, cin, cout, _ptr(bias),
+                                         out.data_ptr(), cout, None, 0, _ptr(st), _stream())
+        _lib.check(rc, "b200ad_upconv3x3")
+        if spi:
+            self.colstats[out.data_ptr()] = (st, 4 * spi, nimg, 4 * h * wd, cout, weakref.ref(out))
+        return out
 
     def attention(self, q, k, v, nbatch, heads, Lq, Lk, d, dpad, kv_div=1, v_ones=False):
         """q/k/v: 2-D operand-typed views (row stride = leading dim).  Returns [nbatch*Lq, heads*d].

@@ -476,6 +476,25 @@ def _mode_of(m: nn.Module) -> str:
     return getattr(m, "_b200_mode", "bf16")
 
 
+def _pack_upconv3x3(o: Ops, w: torch.Tensor) -> torch.Tensor:
+    """torch [cout, cin, 3, 3] -> [4, cout, 4*cin] for b200ad_upconv3x3: phase (py, px) of the nearest-x2 upsampled
+    image sees a 2x2 convolution of the low-resolution image whose tap (ty, tx) is the sum of the 3x3 weights that land
+    on source pixel (y + ty - 1 + py, x + tx - 1 + px): rows ky with floor((py + ky - 1) / 2) == ty - 1 + py.
+    Summed in fp64, rounded to the operand type once; k = (ty*2 + tx)*cin + c."""
+    wd = w.detach().double()
+    cout, cin = wd.shape[:2]
+    rows = {0: ((0,), (1, 2)), 1: ((0, 1), (2,))}      # phase -> (ky of tap 0, ky of tap 1)
+    out = torch.zeros(4, cout, 2, 2, cin, dtype=torch.float64, device=wd.device)
+    for py in (0, 1):
+        for px in (0, 1):
+            for ty in (0, 1):
+                for tx in (0, 1):
+                    for ky in rows[py][ty]:
+                        for kx in rows[px][tx]:
+                            out[py * 2 + px, :, ty, tx] += wd[:, :, ky, kx]
+    return _dev_w(o, out.reshape(4, cout, 4 * cin))
+
+
 def _pack_conv3x3(o: Ops, w: torch.Tensor) -> torch.Tensor:
     """torch [cout, cin, 3, 3] -> [cout, 9*cin] with k = (ky*3+kx)*cin + c (one K block per filter tap)."""
     return _dev_w(o, w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], -1))
@@ -570,7 +589,11 @@ class Upsample2D(_Packable):
         self.conv = Conv2d(channels, channels, 3, padding=1)
 
     def _pack(self, o: Ops):
-        return {"w": _pack_conv3x3(o, self.conv.weight), "b": _dev_f(self.conv.bias)}
+        # bf16 mode: the upsampled image is never formed -- four 2x2 sub-pixel convolutions over the low-resolution
+        # image (4/9 of the MACs; b200ad_upconv3x3).  B200AD_UPCONV=0 (and the fp32 validation mode) keep the direct form.
+        sub = o.mode == "bf16" and os.environ.get("B200AD_UPCONV", "1") != "0"
+        return {"w": None if sub else _pack_conv3x3(o, self.conv.weight), "b": _dev_f(self.conv.bias),
+                "w4": _pack_upconv3x3(o, self.conv.weight) if sub else None}
 
     def forward(self, hidden_states, output_size=None, *a, **kw):
         """Module mode: F.interpolate(scale_factor=2, mode="nearest") (b200ad_cast mode 2) then the conv."""
@@ -581,6 +604,8 @@ class Upsample2D(_Packable):
 
     def run(self, st: _State, x, nimg: int, h: int, w: int):
         o, p = st.o, self.packed(st.o)
+        if p["w4"] is not None:
+            return o.upconv3x3(o.cast(x, nimg, h, w, x.shape[1]), p["w4"], nimg, h, w, bias=p["b"], stats=True)
         up = o.cast(x, nimg, h, w, x.shape[1], mode=2)
         out, _ = o.conv3x3(up, p["w"], nimg, 2 * h, 2 * w, bias=p["b"], stats=True)
         return out

@@ -22,6 +22,7 @@ No CPU fallback, no cuDNN/cuBLAS: every computation is a libb200ad kernel.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Sequence
 
 import torch
@@ -29,7 +30,7 @@ import torch.nn as nn
 
 from .leaf import Conv2d, GroupNorm, Linear, SiLU
 from .ops import Ops, _empty, get_ops
-from .unet import _Packable, _dev_f, _dev_w, _mode_of, _pack_conv3x3
+from .unet import _Packable, _dev_f, _dev_w, _mode_of, _pack_conv3x3, _pack_upconv3x3
 
 
 class _VaeResnet(_Packable):
@@ -161,10 +162,14 @@ class _VaeUpsample(_Packable):
         self.conv = Conv2d(c, c, 3, padding=1)
 
     def _pack(self, o: Ops):
-        return {"w": _pack_conv3x3(o, self.conv.weight), "b": _dev_f(self.conv.bias)}
+        sub = o.mode == "bf16" and os.environ.get("B200AD_UPCONV", "1") != "0"     # see unet.Upsample2D._pack
+        return {"w": None if sub else _pack_conv3x3(o, self.conv.weight), "b": _dev_f(self.conv.bias),
+                "w4": _pack_upconv3x3(o, self.conv.weight) if sub else None}
 
     def run(self, o: Ops, x, n: int, h: int, w: int):
         p = self.packed(o)
+        if p["w4"] is not None:
+            return o.upconv3x3(o.cast(x, n, h, w, x.shape[1]), p["w4"], n, h, w, bias=p["b"], stats=True)
         up = o.cast(x, n, h, w, x.shape[1], mode=2)
         return o.conv3x3(up, p["w"], n, 2 * h, 2 * w, bias=p["b"], stats=True)[0]
 
