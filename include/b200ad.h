@@ -94,6 +94,15 @@ int b200ad_conv3x3_stats(int op_dtype, const void* src, const void* W, int nimg,
                          const float* residual, long long ld_res, float* out_f32, long long ld_o32, float* col_stats,
                          void* stream);
 
+/* ResnetBlock2D.conv2 + conv_shortcut in one launch (`conv_shortcut(input) + conv2(h)`): the 1x1
+ * shortcut is a second K segment of the implicit GEMM -- after the 9*cin tap columns, K continues with the sc_cin
+ * channels of sc_src [nimg, h, w, sc_cin] (operand-typed, unshifted).  W: [cout, 9*cin + sc_cin] = (conv2 weight as
+ * in b200ad_conv3x3 | shortcut weight [cout, sc_cin]); bias = conv2.bias + conv_shortcut.bias.  cin, sc_cin multiples
+ * of 64; bf16 (tcgen05) path, stride 1.  col_stats (optional, fp32-only output) as b200ad_conv3x3_stats. */
+int b200ad_conv3x3_sc(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout,
+                      const void* sc_src, int sc_cin, const float* bias, float* out_f32, long long ld_o32, void* out_op,
+                      long long ld_oop, float* col_stats, void* stream);
+
 /* Upsample2D = F.interpolate(scale_factor=2, mode="nearest") + Conv2d(C, C, 3, padding=1) of the UNet's up blocks and the
  * VAE decoder WITHOUT the upsampled image: four 2x2 convolutions over the low-resolution
  * source, one per output phase (py, px).  src: operand-typed NHWC [nimg, h, w, cin]; outputs are rows of the

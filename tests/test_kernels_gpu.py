@@ -170,6 +170,35 @@ def test_group_norm_is_deterministic_across_launches(mode, c0, c1):
     assert bad == 0, f"{bad} of 300 launches differ from the first"
 
 
+@pytest.mark.parametrize("n,h,w,cin,sc_cin,cout", [(2, 32, 32, 64, 128, 64), (3, 8, 8, 128, 64, 320),
+                                                   (5, 16, 16, 320, 960, 320), (2, 12, 20, 64, 64, 64),
+                                                   (1, 64, 64, 64, 192, 128)])
+def test_conv3x3_with_fused_1x1_shortcut(n, h, w, cin, sc_cin, cout):
+    """b200ad_conv3x3_sc: conv3x3(a) + conv1x1(raw) + bias in one launch (the 1x1 is a second K segment of the implicit
+    GEMM) against the two convolutions in fp32; plus its GroupNorm column statistics."""
+    o = ops("bf16")
+    a = bf(rnd(n, h, w, cin, seed=1))
+    raw = bf(rnd(n, h, w, sc_cin, seed=2))
+    w3 = bf(rnd(cout, cin, 3, 3, seed=3, scale=(9 * cin) ** -0.5))
+    w1 = bf(rnd(cout, sc_cin, 1, 1, seed=4, scale=sc_cin ** -0.5))
+    b = rnd(cout, seed=5) + 0.2
+    ref = (_conv_ref(a, w3, b) + F.conv2d(raw.permute(0, 3, 1, 2), w1).permute(0, 2, 3, 1)).reshape(n * h * w, cout)
+    wcat = torch.cat([_pack_conv(w3), w1.reshape(cout, sc_cin)], 1).contiguous().to(DEV, o.op_dtype)
+    n0 = lib_launches()
+    out = o.conv3x3_sc(a.to(DEV, o.op_dtype).view(n * h * w, cin), wcat, raw.to(DEV, o.op_dtype).view(n * h * w, sc_cin),
+                       n, h, w, bias=b.to(DEV), stats=True)
+    assert lib_launches() - n0 == 1
+    assert rel(out.cpu(), ref) < 2e-5
+    supported = o._stats_ok(True, h, w) > 0
+    assert (out.data_ptr() in o.colstats) == supported
+    if supported:
+        st, spi = o.colstats[out.data_ptr()][:2]
+        tot = st.view(n, spi, cout, 2).sum(1).cpu()
+        per_img = ref.view(n, h * w, cout)
+        assert (tot[..., 0] - per_img.sum(1)).abs().max() < 2e-3 * (h * w) ** 0.5
+        assert rel(tot[..., 1], (per_img ** 2).sum(1)) < 1e-5
+
+
 @pytest.mark.parametrize("n,h,w,cin,cout,exact", [(2, 32, 32, 64, 64, True), (3, 8, 8, 128, 320, True),
                                                   (5, 16, 16, 64, 128, False), (2, 12, 20, 64, 64, False),
                                                   (1, 64, 64, 64, 320, False), (4, 8, 8, 320, 64, True)])

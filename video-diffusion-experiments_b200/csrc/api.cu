@@ -136,17 +136,20 @@ int b200ad_stats_slots(int conv, int h, int w) {
 static int conv_impl(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout, int mode,
                      const float* bias, const float* row_bias, int rb_div, int ld_rb, const float* residual,
                      long long ld_res, float* out_f32, long long ld_o32, void* out_op, long long ld_oop,
-                     float* col_stats, void* stream) {
+                     float* col_stats, void* stream, const void* sc_src = nullptr, int sc_cin = 0) {
   B200AD_REQUIRE(src && W, "conv3x3: null operand");
   B200AD_REQUIRE(out_f32 || out_op, "conv3x3: no output buffer");
   B200AD_REQUIRE(mode == 0 || mode == 1, "conv3x3: mode %d", mode);
   GemmArgs a;
   memset(&a, 0, sizeof(a));
   a.A = src; a.W = W;
-  a.M = nimg * h * w; a.N = cout; a.K = 9 * cin;
+  a.M = nimg * h * w; a.N = cout; a.K = 9 * cin + sc_cin;
   ConvGeom& g = a.conv;
   g.enabled = 1;
   g.nimg = nimg; g.h = h; g.w = w; g.cin = cin; g.ntaps = 9;
+  g.sc_src = sc_src; g.sc_cin = sc_cin;
+  B200AD_REQUIRE(sc_cin == 0 || (op_dtype == 0 && mode == 0 && sc_src),
+                 "conv3x3: the fused 1x1 shortcut exists on the tcgen05 path, stride 1 only");
   g.src_h = h; g.src_w = w;
   g.src_nimg = mode == 0 ? nimg : 4 * nimg;
   for (int ky = 0; ky < 3; ++ky)
@@ -187,6 +190,18 @@ int b200ad_conv3x3_stats(int op_dtype, const void* src, const void* W, int nimg,
   B200AD_REQUIRE(col_stats, "conv3x3_stats: null statistics buffer");
   return conv_impl(op_dtype, src, W, nimg, h, w, cin, cout, mode, bias, row_bias, rb_div, ld_rb, residual, ld_res,
                    out_f32, ld_o32, nullptr, 0, col_stats, stream);
+}
+
+// conv3x3 (stride 1, pad 1) + a 1x1 convolution of a second image accumulated into the same output tile:
+// out = conv3x3(src; W[:, :9cin]) + sc_src W[:, 9cin:]^T + bias (+ row_bias).  ResnetBlock2D.conv2 + conv_shortcut: the
+// shortcut's fp32 result is never written and re-read as a residual.
+int b200ad_conv3x3_sc(int op_dtype, const void* src, const void* W, int nimg, int h, int w, int cin, int cout,
+                      const void* sc_src, int sc_cin, const float* bias, float* out_f32, long long ld_o32, void* out_op,
+                      long long ld_oop, float* col_stats, void* stream) {
+  B200AD_REQUIRE(sc_src && sc_cin > 0, "conv3x3_sc: null shortcut source");
+  B200AD_REQUIRE(!col_stats || (out_f32 && !out_op), "conv3x3_sc: column statistics need an fp32-only output");
+  return conv_impl(op_dtype, src, W, nimg, h, w, cin, cout, 0, bias, nullptr, 1, 0, nullptr, 0, out_f32, ld_o32, out_op,
+                   ld_oop, col_stats, stream, sc_src, sc_cin);
 }
 
 // nearest-x2 upsample followed by conv3x3 (pad 1) as four 2x2 convolutions over the LOW-resolution image, one per output

@@ -19,6 +19,11 @@ struct ConvGeom {
   // this launch is pixel (n, out_scale*y + out_py, out_scale*x + out_px) of an [nimg, out_scale*h, out_scale*w] image.
   // out_scale = 0 or 1: plain output.  Applies to out_f32 / out_op / residual alike (tcgen05 path only).
   int out_scale, out_py, out_px;
+  // Second K segment (a 1x1 convolution accumulated into the same tile: ResnetBlock2D.conv2 + conv_shortcut): after the
+  // ntaps*cin columns of the taps, K continues with sc_cin channels of `sc_src` [nimg, h, w, sc_cin] (operand-typed,
+  // output geometry, no shift).  W is [N, ntaps*cin + sc_cin].  tcgen05 path only.
+  const void* sc_src;
+  int sc_cin;
   // column statistics: slots per image of the whole output (0: the tiles of this launch) and this launch's first slot
   int stats_slots, stats_slot0;
 };

@@ -52,6 +52,7 @@ struct TcParams {
   int n_box, h_box, w_box;
   int tiles_x, tiles_y;
   int cin_blocks;
+  int kb_main;                 // conv: k-blocks that come from the taps; the rest (if any) from EpiMaps::a2
   int tap_dy[9], tap_dx[9], tap_dn[9];
   // epilogue
   int has_res, has_o32, has_oop, geglu;
@@ -209,6 +210,7 @@ __device__ __forceinline__ void sts_u4(uint32_t a, uint32_t x, uint32_t y, uint3
 
 struct EpiMaps {
   CUtensorMap res, o32, oop;
+  CUtensorMap a2;              // conv: source of the second K segment (ConvGeom::sc_src)
 };
 
 // Elected epilogue thread: make chunk buffer `buf` of group `g` ready for chunk `cur` (fetch its residual, or
@@ -305,6 +307,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (f_res) tma_prefetch_desc(&em.res);
     if (f_o32) tma_prefetch_desc(&em.o32);
     if (f_oop) tma_prefetch_desc(&em.oop);
+    if (p.conv && p.kb_main < p.num_kb) tma_prefetch_desc(&em.a2);
     for (int s = 0; s < p.num_stages; ++s) {
       mbar_init(&full_bar[s], 2);        // the leader's A producer and W producer each arrive with their tx bytes
       mbar_init(&empty_bar[s], 1);
@@ -350,14 +353,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
           if (elect_one()) {
             if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2u * A_STAGE_BYTES);
-            if (p.conv)
-              tma2_load_4d(sa, &tmA, fb0 + 8u * stage, cb * BK, t.x0 + p.tap_dx[tap], t.y0 + p.tap_dy[tap],
-                           t.n0 + p.tap_dn[tap]);
-            else
+            if (p.conv) {
+              if (kb < p.kb_main)
+                tma2_load_4d(sa, &tmA, fb0 + 8u * stage, cb * BK, t.x0 + p.tap_dx[tap], t.y0 + p.tap_dy[tap],
+                             t.n0 + p.tap_dn[tap]);
+              else
+                tma2_load_4d(sa, &em.a2, fb0 + 8u * stage, (kb - p.kb_main) * BK, t.x0, t.y0, t.n0);
+            } else
               tma2_load_2d(sa, &tmA, fb0 + 8u * stage, kb * BK, t.m_tile * BM);
           }
           __syncwarp();
-          if (p.conv && ++cb == p.cin_blocks) { cb = 0; ++tap; }
+          if (p.conv && kb < p.kb_main && ++cb == p.cin_blocks) { cb = 0; ++tap; }
           if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -795,7 +801,10 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     B200AD_REQUIRE(g.cin % BK == 0, "conv: cin=%d must be a multiple of %d on the tcgen05 path", g.cin, BK);
     B200AD_REQUIRE(g.n_box * g.h_box * g.w_box == BM, "conv: tile box %dx%dx%d != %d rows", g.n_box, g.h_box,
                    g.w_box, BM);
-    B200AD_REQUIRE(a.K == g.ntaps * g.cin, "conv: K=%d != ntaps*cin=%d", a.K, g.ntaps * g.cin);
+    B200AD_REQUIRE(a.K == g.ntaps * g.cin + g.sc_cin, "conv: K=%d != ntaps*cin + sc_cin = %d", a.K,
+                   g.ntaps * g.cin + g.sc_cin);
+    B200AD_REQUIRE(g.sc_cin == 0 || (g.sc_src && g.sc_cin % BK == 0),
+                   "conv: the second K segment needs a source and a multiple of %d channels (got %d)", BK, g.sc_cin);
     B200AD_REQUIRE(a.M == g.nimg * g.h * g.w, "conv: M=%d != nimg*h*w", a.M);
     B200AD_REQUIRE(g.out_scale <= 1 || !e.row_bias, "conv: a row bias cannot be combined with a sub-pixel output");
     p.conv = 1;
@@ -805,6 +814,13 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     p.tiles_y = (g.h + g.h_box - 1) / g.h_box;
     num_m_tiles = p.tiles_x * p.tiles_y * ((g.nimg + g.n_box - 1) / g.n_box);
     p.cin_blocks = g.cin / BK;
+    p.kb_main = g.ntaps * p.cin_blocks;
+    if (g.sc_cin > 0) {
+      uint64_t d2[4] = {(uint64_t)g.sc_cin, (uint64_t)g.w, (uint64_t)g.h, (uint64_t)g.nimg};
+      uint64_t s2[3] = {(uint64_t)g.sc_cin * 2, (uint64_t)g.w * g.sc_cin * 2, (uint64_t)g.h * g.w * g.sc_cin * 2};
+      uint32_t b2[4] = {(uint32_t)BK, (uint32_t)g.w_box, (uint32_t)g.h_box, (uint32_t)g.n_box};
+      if (int rc = make_tmap_bf16(&em.a2, g.sc_src, 4, d2, s2, b2)) return rc;
+    }
     for (int t = 0; t < 9; ++t) { p.tap_dy[t] = g.tap_dy[t]; p.tap_dx[t] = g.tap_dx[t]; p.tap_dn[t] = g.tap_dn[t]; }
     uint64_t dims[4] = {(uint64_t)g.cin, (uint64_t)g.src_w, (uint64_t)g.src_h, (uint64_t)g.src_nimg};
     uint64_t strides[3] = {(uint64_t)g.cin * 2, (uint64_t)g.src_w * g.cin * 2, (uint64_t)g.src_h * g.src_w * g.cin * 2};

@@ -30,6 +30,7 @@ SIGNATURES = {
     "b200ad_gn_stats_ws_bytes": [_I, _I, _I],
     "b200ad_gemm_stats": [_I, _P, _L, _P, _I, _I, _I, _P, _P, _I, _I, _P, _L, _P, _L, _P, _I, _P],
     "b200ad_conv3x3_stats": [_I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _I, _I, _P, _L, _P, _L, _P, _P],
+    "b200ad_conv3x3_sc": [_I, _P, _P, _I, _I, _I, _I, _I, _P, _I, _P, _P, _L, _P, _L, _P, _P],
     "b200ad_upconv3x3": [_I, _P, _P, _I, _I, _I, _I, _I, _P, _P, _L, _P, _L, _P, _P],
     "b200ad_gn_apply_stats": [_I, _P, _I, _P, _I, _P, _I, _P, _I, _I, _I, _I, _I, _F, _P, _P, _I, _P, _P, _P, _P],
     "b200ad_gn_counters_nonzero": [],

@@ -192,6 +192,29 @@ class Ops:
         _lib.check(rc, "b200ad_conv3x3")
         return out_f32, out_op
 
+    def conv3x3_sc(self, src, w, sc_src, nimg, h, wd, *, bias=None, stats=False):
+        """conv3x3(src) + 1x1 conv of sc_src accumulated in the same tiles (b200ad_conv3x3_sc): w [cout, 9*cin + sc_cin],
+        src [nimg*h*wd, cin], sc_src [nimg*h*wd, sc_cin], both operand-typed.  Returns the fp32 rows.  bf16 mode only."""
+        _need_cuda(src, w, sc_src)
+        assert self.op == BF16, "conv3x3_sc exists on the tcgen05 path only"
+        assert src.dtype == self.op_dtype and w.dtype == self.op_dtype and sc_src.dtype == self.op_dtype
+        assert src.is_contiguous() and w.is_contiguous() and sc_src.is_contiguous()
+        cout, ktot = w.shape
+        cin, sc_cin = src.shape[1], sc_src.shape[1]
+        assert ktot == 9 * cin + sc_cin
+        M = nimg * h * wd
+        out = _empty((M, cout), src.device, torch.float32)
+        spi = self._stats_ok(True, h, wd) if stats else 0
+        st = _empty((nimg * spi, cout, 2), src.device, torch.float32) if spi else None
+        with self._rec("conv3x3", 2.0 * M * cout * ktot, _nb(src, sc_src, w, out, st)):
+            rc = self.L.b200ad_conv3x3_sc(self.op, src.data_ptr(), w.data_ptr(), nimg, h, wd, cin, cout,
+                                          sc_src.data_ptr(), sc_cin, _ptr(bias), out.data_ptr(), cout, None, 0,
+                                          _ptr(st), _stream())
+        _lib.check(rc, "b200ad_conv3x3_sc")
+        if spi:
+            self.colstats[out.data_ptr()] = (st, spi, nimg, h * wd, cout, weakref.ref(out))
+        return out
+
     def upconv3x3(self, src, w4, nimg, h, wd, *, bias=None, stats=False):
         """nearest-x2 upsample + 3x3 conv of the low-resolution NHWC `src` [nimg*h*wd, cin] (operand-typed) as four
         2x2 sub-pixel convolutions (b200ad_upconv3x3); w4 [4, cout, 4*cin] from pack_upconv_weights().  Returns the

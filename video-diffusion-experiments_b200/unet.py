@@ -525,6 +525,11 @@ class ResnetBlock2D(_Packable):
         if self.conv_shortcut is not None:
             w = self.conv_shortcut.weight
             p["wsc"], p["bsc"] = _dev_w(o, w.reshape(w.shape[0], w.shape[1])), _dev_f(self.conv_shortcut.bias)
+            # bf16 mode: the 1x1 shortcut rides along as a second K segment of conv2's implicit GEMM
+            # (b200ad_conv3x3_sc), its fp32 result is never written / re-read.  B200AD_CONV_SC=0 keeps two launches.
+            if o.mode == "bf16" and self.in_channels % 64 == 0 and os.environ.get("B200AD_CONV_SC", "1") != "0":
+                p["w2sc"] = torch.cat([p["w2"], p["wsc"]], 1).contiguous()
+                p["b2sc"] = p["cb2"] + p["bsc"]
         return p
 
     def run(self, st: _State, x, skip, nimg: int, h: int, w: int, temb_proj=None):
@@ -542,6 +547,8 @@ class ResnetBlock2D(_Packable):
             a, raw = a
         h32, _ = o.conv3x3(a, p["w1"], nimg, h, w, bias=p["cb1"], row_bias=temb_proj, rb_div=rb_div, stats=True)
         a2 = o.group_norm(h32, None, nimg, hw, G, p["g2"], p["b2"], self.norm2.eps, silu=True)
+        if need_raw and "w2sc" in p:
+            return o.conv3x3_sc(a2, p["w2sc"], raw, nimg, h, w, bias=p["b2sc"], stats=True)
         if need_raw:
             res, _ = o.gemm(raw, p["wsc"], bias=p["bsc"], want_f32=True)
         else:

@@ -55,6 +55,9 @@ class _VaeResnet(_Packable):
         if self.conv_shortcut is not None:
             w = self.conv_shortcut.weight
             p["wsc"], p["bsc"] = _dev_w(o, w.reshape(w.shape[0], w.shape[1])), _dev_f(self.conv_shortcut.bias)
+            if o.mode == "bf16" and self.in_channels % 64 == 0 and os.environ.get("B200AD_CONV_SC", "1") != "0":
+                p["w2sc"] = torch.cat([p["w2"], p["wsc"]], 1).contiguous()      # see unet.ResnetBlock2D._pack
+                p["b2sc"] = p["cb2"] + p["bsc"]
         return p
 
     def run(self, o: Ops, x, n: int, h: int, w: int):
@@ -70,6 +73,8 @@ class _VaeResnet(_Packable):
         del a
         a2 = o.group_norm(h32, None, n, h * w, G, p["g2"], p["b2"], self.norm2.eps, silu=True)
         del h32
+        if need_raw and "w2sc" in p:
+            return o.conv3x3_sc(a2, p["w2sc"], raw, n, h, w, bias=p["b2sc"], stats=True)
         res = o.gemm(raw, p["wsc"], bias=p["bsc"], want_f32=True)[0] if need_raw else x
         out, _ = o.conv3x3(a2, p["w2"], n, h, w, bias=p["cb2"], residual=res, stats=True)
         return out
