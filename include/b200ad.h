@@ -131,8 +131,10 @@ int b200ad_cast(int op_dtype, const float* x, int nimg, int h, int w, int C, int
 
 /* ---- K3/K4: spatial self-attention and text cross-attention (replaces F.scaled_dot_product_attention in
  * AttnProcessor2_0).  q/k/v: operand-typed, head `hd` of batch item n at q[(n*Lq + i)*ldq + hd*dpad + j];
- * k/v batch index = n / kv_div (text K/V shared by the frames of a batch item).  dpad >= d is the padded head
- * width (64/128/192 on the tcgen05 path, pad columns zero); out_op[(n*Lq+i)*ldo + hd*d + j], softmax scale = d^-1/2. */
+ * k/v batch index = n / kv_div (text K/V shared by the frames of a batch item).  dpad = head stride in the rows: on
+ * the tcgen05 path a multiple of 8 with 16*ceil(d/16) <= dpad <= 192, columns d..dpad-1 of q and k zero (the kernels
+ * load 64-column slabs, which may run into the next head, but use 16*ceil(d/16) columns of q/k and d (+1) of v only);
+ * out_op[(n*Lq+i)*ldo + hd*d + j], softmax scale = d^-1/2. */
 int b200ad_attention(int op_dtype, const void* q, long long ldq, const void* k, long long ldk, const void* v,
                      long long ldv, int nbatch, int heads, int Lq, int Lk, int d, int dpad, int kv_div,
                      void* out_op, long long ldo, void* stream);

@@ -352,7 +352,12 @@ def _attn_ref(q, k, v):
     # benchmarked lengths without the V ones column (the in-kernel row-sum path): config 2 and config 5 level 0
     (2, 2, 4096, 4096, 40, 64, 1), (1, 1, 9216, 9216, 40, 64, 1),
     # single key tile (persistent cross-attention kernel): ragged query count, key counts 16 / 50 / 128, many tiles per CTA
-    (3, 2, 200, 50, 40, 64, 1), (2, 4, 384, 128, 80, 128, 2), (2, 2, 640, 16, 160, 192, 1), (16, 8, 4096, 77, 40, 64, 16)])
+    (3, 2, 200, 50, 40, 64, 1), (2, 4, 384, 128, 80, 128, 2), (2, 2, 640, 16, 160, 192, 1), (16, 8, 4096, 77, 40, 64, 16),
+    # tight head strides (48 / 88 / 168 instead of whole 64-column slabs: a slab then runs into the next head, whose
+    # columns no MMA may use) on every kernel: ping-pong, single-key-tile, short-sequence
+    (2, 8, 256, 256, 40, 48, 1), (3, 2, 1024, 1024, 40, 48, 1), (2, 8, 64, 64, 160, 168, 1), (2, 4, 256, 256, 80, 88, 1),
+    (4, 8, 256, 77, 40, 48, 2), (2, 8, 64, 77, 160, 168, 2), (2, 8, 1024, 77, 80, 88, 1), (2, 2, 1024, 1024, 80, 88, 1),
+    (2, 3, 4096, 4096, 40, 48, 1), (1, 2, 200, 300, 8, 16, 1), (2, 8, 256, 256, 160, 160, 1)])
 def test_attention(mode, tol, nb, heads, Lq, Lk, d, dpad, kv_div):
     o = ops(mode)
     nkv = nb // kv_div
@@ -378,7 +383,10 @@ def test_attention(mode, tol, nb, heads, Lq, Lk, d, dpad, kv_div):
                                                     # the exact instance of the bench (config 2 level 0: L = 4096, d = 40,
                                                     # three query tiles per CTA, ragged last CTA) and config 5 (L = 9216)
                                                     (4, 8, 4096, 40, 64, False), (1, 2, 9216, 40, 64, False),
-                                                    (1, 4, 4096, 80, 128, False)])
+                                                    (1, 4, 4096, 80, 128, False),
+                                                    # tight head strides: the stride the UNet uses (unet._dpad)
+                                                    (4, 8, 4096, 40, 48, False), (1, 3, 2304, 80, 88, False),
+                                                    (1, 2, 1024, 40, 48, True), (2, 8, 256, 40, 48, False)])
 def test_attention_denominator_from_ones_column(nb, heads, L, d, dpad, grow):
     """B200AD_ATTN_V_ONES: V's pad column d holds 1.0, the long self-attention kernel takes the softmax denominator
     from the PV product (incl. across lazy rescales); the short-sequence kernel (L = 256) must simply ignore it."""

@@ -38,6 +38,8 @@ struct FaParams {
   int Lq, Lk, d, nkv;
   int stagger;             // tile B starts its first exponent phase after tile A's (initial anti-phase offset)
   int dk16;                // k-steps of 16 for Q K^T
+  int hs;                  // head stride in the q/k/v rows (elements): 16*dk16 <= hs <= DP; a 64-column slab may run
+                           // into the next head, whose columns the MMAs never use (QK^T stops at 16*dk16, O beyond d is not read)
   float scale_log2;        // d^-1/2 * log2(e)
   bf16* out;
   long long ldo;
@@ -188,7 +190,7 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
       for (int t = 0; t < NT; ++t)
 #pragma unroll
         for (int s = 0; s < NS; ++s)
-          tma_load_3d(sQ + (t * NS + s) * QSLAB, &tmQ, q_full, hd * DP + s * 64, (NT * qt + t) * 128, n);
+          tma_load_3d(sQ + (t * NS + s) * QSLAB, &tmQ, q_full, hd * p.hs + s * 64, (NT * qt + t) * 128, n);
     }
     __syncwarp();
     int st = 0;
@@ -199,8 +201,8 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mbar_arrive_expect_tx(&kv_full[st], 2 * NS * KSLAB);
 #pragma unroll
         for (int s = 0; s < NS; ++s) {
-          tma_load_3d(sK + (st * NS + s) * KSLAB, &tmK, &kv_full[st], hd * DP + s * 64, j * BN, n);
-          tma_load_3d(sV + (st * NS + s) * KSLAB, &tmV, &kv_full[st], hd * DP + s * 64, j * BN, n);
+          tma_load_3d(sK + (st * NS + s) * KSLAB, &tmK, &kv_full[st], hd * p.hs + s * 64, j * BN, n);
+          tma_load_3d(sV + (st * NS + s) * KSLAB, &tmV, &kv_full[st], hd * p.hs + s * 64, j * BN, n);
         }
       }
       __syncwarp();
@@ -497,10 +499,10 @@ attn_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 
 template <int DP, int BN, bool VS, int TPR, bool PT, int NT = 2>
 static int launch_attn_fa(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
-                          int nbatch, int heads, int L, int d, void* out, long long ldo, cudaStream_t stream) {
+                          int nbatch, int heads, int L, int d, int hs, void* out, long long ldo, cudaStream_t stream) {
   constexpr int NS = DP / 64;
   CUtensorMap tmQ, tmK, tmV;
-  uint64_t dims[3] = {(uint64_t)heads * DP, (uint64_t)L, (uint64_t)nbatch};
+  uint64_t dims[3] = {(uint64_t)heads * hs, (uint64_t)L, (uint64_t)nbatch};
   {
     uint64_t str[2] = {(uint64_t)ldq * 2, (uint64_t)L * ldq * 2};
     uint32_t box[3] = {64, 128, 1};
@@ -522,6 +524,7 @@ static int launch_attn_fa(const void* q, long long ldq, const void* k, long long
   p.stagger = 1;
   p.dbg = g_fa_dbg;
   p.dk16 = (d + 15) / 16;
+  p.hs = hs;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)d);
   p.out = reinterpret_cast<bf16*>(out);
   p.ldo = ldo;
@@ -551,12 +554,13 @@ int attention_bf16_fa(const void* q, long long ldq, const void* k, long long ldk
   // the ones that did not -- two softmax threads per row, P through shared memory, speculative exponentials, other tile
   // counts; their launch paths and environment switches are gone).  One softmax thread per row, P in tensor memory;
   // d <= 64 with the V ones column: three query tiles per CTA (1.56 vs 1.62-1.70 ms at L=4096 d=40), else two.
-  if (dpad == 64)
-    return vs ? launch_attn_fa<64, 64, true, 1, true, 3>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
-              : launch_attn_fa<64, 128, false, 1, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
-  if (dpad == 128)
-    return vs ? launch_attn_fa<128, 64, true, 1, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream)
-              : launch_attn_fa<128, 64, false, 1, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, out, ldo, stream);
+  if (dpad % 8 != 0 || dpad < 16 * ((d + 15) / 16)) return 1;       // head stride: see FaParams::hs
+  if (dpad <= 64)
+    return vs ? launch_attn_fa<64, 64, true, 1, true, 3>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, dpad, out, ldo, stream)
+              : launch_attn_fa<64, 128, false, 1, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, dpad, out, ldo, stream);
+  if (dpad <= 128)
+    return vs ? launch_attn_fa<128, 64, true, 1, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, dpad, out, ldo, stream)
+              : launch_attn_fa<128, 64, false, 1, true, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, d, dpad, out, ldo, stream);
   return 1;
 }
 

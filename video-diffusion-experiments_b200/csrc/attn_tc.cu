@@ -26,6 +26,8 @@ static constexpr int SLAB = 128 * 128;   // bytes of one [128 rows x 64 bf16] sw
 
 struct AttnParams {
   int Lq, Lk, d, kv_div, nkv;
+  int dk16;                // k-steps of 16 for Q K^T
+  int hs;                  // head stride in the q/k/v rows (see FaParams::hs in attn_fa.cu)
   float scale_log2;        // d^-1/2 * log2(e)
   bf16* out;
   long long ldo;
@@ -88,7 +90,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     if (lane == 0) {
       mbar_arrive_expect_tx(q_full, NS * SLAB);
 #pragma unroll
-      for (int s = 0; s < NS; ++s) tma_load_3d(sQ + s * SLAB, &tmQ, q_full, hd * DP + s * 64, qt * 128, n);
+      for (int s = 0; s < NS; ++s) tma_load_3d(sQ + s * SLAB, &tmQ, q_full, hd * p.hs + s * 64, qt * 128, n);
       const int nkvb = n / p.kv_div;
       for (int j = 0; j < p.nkv; ++j) {
         const int st = j % NST;
@@ -96,8 +98,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         mbar_arrive_expect_tx(&kv_full[st], 2 * NS * SLAB);
 #pragma unroll
         for (int s = 0; s < NS; ++s) {
-          tma_load_3d(sK + (st * NS + s) * SLAB, &tmK, &kv_full[st], hd * DP + s * 64, j * 128, nkvb);
-          tma_load_3d(sV + (st * NS + s) * SLAB, &tmV, &kv_full[st], hd * DP + s * 64, j * 128, nkvb);
+          tma_load_3d(sK + (st * NS + s) * SLAB, &tmK, &kv_full[st], hd * p.hs + s * 64, j * 128, nkvb);
+          tma_load_3d(sV + (st * NS + s) * SLAB, &tmV, &kv_full[st], hd * p.hs + s * 64, j * 128, nkvb);
         }
       }
     }
@@ -114,7 +116,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         tc_fence_after();
         // S = Q K^T  (K-major A and B; K dimension = head width DP, 16 per instruction)
 #pragma unroll
-        for (int kk = 0; kk < DP / 16; ++kk) {
+        for (int kk = 0; kk < p.dk16; ++kk) {
           const uint64_t adesc = umma_desc_k_sw128(smem_u32(sQ + (kk / 4) * SLAB)) + (uint64_t)(2 * (kk % 4));
           const uint64_t bdesc =
               umma_desc_k_sw128(smem_u32(sK + (st * NS + kk / 4) * SLAB)) + (uint64_t)(2 * (kk % 4));
@@ -247,19 +249,19 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 
 template <int DP, int NST>
 static int launch_attn_tc(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
-                          int nbatch, int heads, int Lq, int Lk, int d, int kv_div, void* out, long long ldo,
+                          int nbatch, int heads, int Lq, int Lk, int d, int hs, int kv_div, void* out, long long ldo,
                           cudaStream_t stream) {
   constexpr int NS = DP / 64;
   CUtensorMap tmQ, tmK, tmV;
   const int nkvb = (nbatch + kv_div - 1) / kv_div;
   {
-    uint64_t dims[3] = {(uint64_t)heads * DP, (uint64_t)Lq, (uint64_t)nbatch};
+    uint64_t dims[3] = {(uint64_t)heads * hs, (uint64_t)Lq, (uint64_t)nbatch};
     uint64_t str[2] = {(uint64_t)ldq * 2, (uint64_t)Lq * ldq * 2};
     uint32_t box[3] = {64, 128, 1};
     if (int rc = make_tmap_bf16(&tmQ, q, 3, dims, str, box)) return rc;
   }
   {
-    uint64_t dims[3] = {(uint64_t)heads * DP, (uint64_t)Lk, (uint64_t)nkvb};
+    uint64_t dims[3] = {(uint64_t)heads * hs, (uint64_t)Lk, (uint64_t)nkvb};
     uint64_t str[2] = {(uint64_t)ldk * 2, (uint64_t)Lk * ldk * 2};
     uint32_t box[3] = {64, 128, 1};
     if (int rc = make_tmap_bf16(&tmK, k, 3, dims, str, box)) return rc;
@@ -269,6 +271,8 @@ static int launch_attn_tc(const void* q, long long ldq, const void* k, long long
   AttnParams p;
   p.Lq = Lq; p.Lk = Lk; p.d = d; p.kv_div = kv_div;
   p.nkv = (Lk + 127) / 128;
+  p.dk16 = (d + 15) / 16;
+  p.hs = hs;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)d);
   p.out = reinterpret_cast<bf16*>(out);
   p.ldo = ldo;
@@ -320,14 +324,16 @@ extern "C" int b200ad_attention2(int op_dtype, const void* q, long long ldq, con
     if (rc <= 0) return rc;          // single key tile: the persistent kernel of attn_x.cu
   }
   const bool one_tile = Lk <= 128;
-  if (dpad == 64)
-    return one_tile ? launch_attn_tc<64, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st)
-                    : launch_attn_tc<64, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
-  if (dpad == 128)
-    return one_tile ? launch_attn_tc<128, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st)
-                    : launch_attn_tc<128, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
-  if (dpad == 192)
-    return launch_attn_tc<192, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out_op, ldo, st);
-  set_error("attention: dpad=%d unsupported on the tcgen05 path (64, 128, 192)", dpad);
+  B200AD_REQUIRE(dpad % 8 == 0 && dpad >= 16 * ((d + 15) / 16),
+                 "attention: head stride %d must be a multiple of 8 and >= %d", dpad, 16 * ((d + 15) / 16));
+  if (dpad <= 64)
+    return one_tile ? launch_attn_tc<64, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out_op, ldo, st)
+                    : launch_attn_tc<64, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out_op, ldo, st);
+  if (dpad <= 128)
+    return one_tile ? launch_attn_tc<128, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out_op, ldo, st)
+                    : launch_attn_tc<128, 2>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out_op, ldo, st);
+  if (dpad <= 192)
+    return launch_attn_tc<192, 1>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out_op, ldo, st);
+  set_error("attention: head stride %d unsupported on the tcgen05 path (<= 192)", dpad);
   return -1;
 }

@@ -26,6 +26,7 @@ static constexpr int QSLAB_X = 128 * 128;      // [128 rows x 64 bf16] swizzled 
 
 struct AxParams {
   int Lq, Lk, d, kv_div, KB, ntiles, dk16;
+  int hs;                  // head stride in the q/k/v rows (see FaParams::hs in attn_fa.cu)
   float scale_log2;        // d^-1/2 * log2(e)
   bf16* out;
   long long ldo;
@@ -99,8 +100,8 @@ attn_x_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
       mbar_arrive_expect_tx(kv_full, 2 * NS * KSLAB);
 #pragma unroll
       for (int s = 0; s < NS; ++s) {
-        tma_load_3d(sK + s * KSLAB, &tmK, kv_full, hd * DP + s * 64, 0, nkvb);
-        tma_load_3d(sV + s * KSLAB, &tmV, kv_full, hd * DP + s * 64, 0, nkvb);
+        tma_load_3d(sK + s * KSLAB, &tmK, kv_full, hd * p.hs + s * 64, 0, nkvb);
+        tma_load_3d(sV + s * KSLAB, &tmV, kv_full, hd * p.hs + s * 64, 0, nkvb);
       }
       int st = 0;
       uint32_t ph = 0;
@@ -109,7 +110,7 @@ attn_x_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
         mbar_arrive_expect_tx(&q_full[st], NS * QSLAB_X);
 #pragma unroll
         for (int s = 0; s < NS; ++s)
-          tma_load_3d(sQ + (st * NS + s) * QSLAB_X, &tmQ, &q_full[st], hd * DP + s * 64, qt * 128, n);
+          tma_load_3d(sQ + (st * NS + s) * QSLAB_X, &tmQ, &q_full[st], hd * p.hs + s * 64, qt * 128, n);
         if (++st == AX_QST) { st = 0; ph ^= 1; }
       }
     }
@@ -265,20 +266,20 @@ attn_x_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
 
 template <int DP, int KBT, bool LAST_ONLY>
 static int launch_attn_x(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
-                         int nbatch, int heads, int Lq, int Lk, int d, int kv_div, void* out, long long ldo,
+                         int nbatch, int heads, int Lq, int Lk, int d, int hs, int kv_div, void* out, long long ldo,
                          cudaStream_t stream) {
   constexpr int NS = DP / 64;
   constexpr int KB = KBT;
   CUtensorMap tmQ, tmK, tmV;
   const int nkvb = (nbatch + kv_div - 1) / kv_div;
   {
-    uint64_t dims[3] = {(uint64_t)heads * DP, (uint64_t)Lq, (uint64_t)nbatch};
+    uint64_t dims[3] = {(uint64_t)heads * hs, (uint64_t)Lq, (uint64_t)nbatch};
     uint64_t str[2] = {(uint64_t)ldq * 2, (uint64_t)Lq * ldq * 2};
     uint32_t box[3] = {64, 128, 1};
     if (int rc = make_tmap_bf16(&tmQ, q, 3, dims, str, box)) return rc;
   }
   {
-    uint64_t dims[3] = {(uint64_t)heads * DP, (uint64_t)Lk, (uint64_t)nkvb};
+    uint64_t dims[3] = {(uint64_t)heads * hs, (uint64_t)Lk, (uint64_t)nkvb};
     uint64_t str[2] = {(uint64_t)ldk * 2, (uint64_t)Lk * ldk * 2};
     uint32_t box[3] = {64, (uint32_t)KB, 1};
     if (int rc = make_tmap_bf16(&tmK, k, 3, dims, str, box)) return rc;
@@ -289,6 +290,7 @@ static int launch_attn_x(const void* q, long long ldq, const void* k, long long 
   p.Lq = Lq; p.Lk = Lk; p.d = d; p.kv_div = kv_div; p.KB = KB;
   p.ntiles = (Lq + 127) / 128;
   p.dk16 = (d + 15) / 16;
+  p.hs = hs;
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)d);
   p.out = reinterpret_cast<bf16*>(out);
   p.ldo = ldo;
@@ -324,14 +326,15 @@ int attention_bf16_x(const void* q, long long ldq, const void* k, long long ldk,
 #define AX_LAUNCH(DPV)                                                                                              \
   do {                                                                                                              \
     if (Lk <= 80)                                                                                                   \
-      return Lk > 64 ? launch_attn_x<DPV, 80, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream)   \
-                     : launch_attn_x<DPV, 80, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream); \
-    return Lk > 112 ? launch_attn_x<DPV, 128, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream)   \
-                    : launch_attn_x<DPV, 128, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, kv_div, out, ldo, stream); \
+      return Lk > 64 ? launch_attn_x<DPV, 80, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out, ldo, stream)   \
+                     : launch_attn_x<DPV, 80, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out, ldo, stream); \
+    return Lk > 112 ? launch_attn_x<DPV, 128, true>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out, ldo, stream)   \
+                    : launch_attn_x<DPV, 128, false>(q, ldq, k, ldk, v, ldv, nbatch, heads, Lq, Lk, d, dpad, kv_div, out, ldo, stream); \
   } while (0)
-  if (dpad == 64) AX_LAUNCH(64);
-  if (dpad == 128) AX_LAUNCH(128);
-  if (dpad == 192) AX_LAUNCH(192);
+  if (dpad % 8 != 0 || dpad < 16 * ((d + 15) / 16)) return 1;
+  if (dpad <= 64) AX_LAUNCH(64);
+  if (dpad <= 128) AX_LAUNCH(128);
+  if (dpad <= 192) AX_LAUNCH(192);
 #undef AX_LAUNCH
   return 1;
 }

@@ -63,13 +63,18 @@ class Transformer2DModelOutput:
 
 
 def _dpad(d: int, o: Ops) -> int:
-    """Padded head width of the tcgen05 attention kernel (64-column swizzle slabs); fp32 mode needs none."""
+    """Head stride of q/k/v in the rows the tcgen05 attention kernels read; fp32 mode needs none.  The kernels load
+    64-column slabs but only use 16*ceil(d/16) columns of Q/K and d (+1: the ones column) columns of V/O, so the stride
+    is just wide enough for those -- 48 / 88 / 168 for d = 40 / 80 / 160 instead of 64 / 128 / 192: a quarter less QKV
+    GEMM work and q/k/v traffic.  B200AD_TIGHT_HEADS=0: pad to whole slabs."""
     if o.mode == "fp32":
         return d
-    for p in (64, 128, 192):
-        if d <= p:
-            return p
-    raise ValueError(f"head dim {d} > 192 unsupported")
+    if d > 192:
+        raise ValueError(f"head dim {d} > 192 unsupported")
+    slab = next(p for p in (64, 128, 192) if d <= p)
+    if os.environ.get("B200AD_TIGHT_HEADS", "1") == "0":
+        return slab
+    return min(slab, max((d + 15) // 16 * 16, (d + 1 + 7) // 8 * 8))
 
 
 def _dev_w(o: Ops, w: torch.Tensor) -> torch.Tensor:
