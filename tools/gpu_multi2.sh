@@ -27,7 +27,9 @@ if [ "$N" = "2" ]; then
       > $out/bench_${tag}_config3_n2.json 2> $out/bench_${tag}_config3_n2.err; echo "config3 exit $?"
   last $out/bench_${tag}_config3_n2.json
 fi
-for mode in "pairs overlapped:" "replicas overlapped:--no-pairs" "pairs synchronous:--sync-export"; do
+modes=("pairs overlapped:" "replicas overlapped:--no-pairs" "pairs synchronous:--sync-export")
+[ -n "$SKIP_SYNC" ] && modes=("pairs overlapped:" "replicas overlapped:--no-pairs")     # the stall comparison is not re-measured
+for mode in "${modes[@]}"; do
   name=${mode%%:*}; flag=${mode#*:}; d=$out/sweep_${tag}_$(echo $name | tr ' ' '_')
   rm -rf $d
   timeout 900 bash -c "$(declare -f run); N=$N run 29543 -m b200ad.sweep --output $d --limit $LIMIT $flag" \
