@@ -244,3 +244,62 @@ def test_sweep_exporter_writes_the_reference_layout(tmp_path):
     assert (exp / f"{run.experiment_id}.gif").exists() and sweep.is_done(run, tmp_path)
     from PIL import Image
     assert np.array_equal(np.asarray(Image.open(exp / "frames" / "frame_0001.png")), arr[1])
+
+
+def test_subpixel_upsample_weights_reproduce_upsample_then_conv():
+    """unet.upconv_weights (what b200ad_upconv3x3 consumes): nearest x2 + conv3x3(pad 1) == four 2x2 convolutions of the
+    low-resolution image, phase (py, px) reading source pixels (y + ty - 1 + py, x + tx - 1 + px) -- checked in fp64 on
+    the CPU, borders included (the kernel's TMA zero fill = the zero padding of the upsampled image)."""
+    import torch.nn.functional as F
+    from b200ad.unet import upconv_weights
+    g = torch.Generator().manual_seed(0)
+    n, cin, cout, h, w = 2, 5, 3, 4, 6
+    x = torch.randn(n, cin, h, w, generator=g, dtype=torch.float64)
+    wt = torch.randn(cout, cin, 3, 3, generator=g, dtype=torch.float64)
+    ref = F.conv2d(F.interpolate(x, scale_factor=2.0, mode="nearest"), wt, padding=1)          # [n, cout, 2h, 2w]
+    w4 = upconv_weights(wt).reshape(4, cout, 2, 2, cin)
+    xp = F.pad(x, (1, 1, 1, 1))                                                                # zero halo
+    out = torch.zeros_like(ref)
+    for py in (0, 1):
+        for px in (0, 1):
+            acc = torch.zeros(n, cout, h, w, dtype=torch.float64)
+            for ty in (0, 1):
+                for tx in (0, 1):
+                    dy, dx = ty - 1 + py, tx - 1 + px
+                    src = xp[:, :, 1 + dy:1 + dy + h, 1 + dx:1 + dx + w]
+                    acc += torch.einsum("oc,nchw->nohw", w4[py * 2 + px, :, ty, tx], src)
+            out[:, :, py::2, px::2] = acc
+    assert (out - ref).abs().max() < 1e-12
+
+
+def test_fold_tail_weights_equal_ff2_then_proj_out():
+    """unet.fold_tail_weights: x + Wout (h + W2 g + b2) + bout == x + [h | g] [Wout | Wout W2]^T + (Wout b2 + bout)."""
+    from b200ad.unet import fold_tail_weights
+    g = torch.Generator().manual_seed(1)
+    C, M = 8, 11
+    r = lambda *s: torch.randn(*s, generator=g, dtype=torch.float64)
+    w2, b2, wo, bo = r(C, 4 * C), r(C), r(C, C, 1, 1), r(C)                  # proj_out as a 1x1 conv weight
+    x, h, gate = r(M, C), r(M, C), r(M, 4 * C)
+    ref = x + (h + gate @ w2.T + b2) @ wo.reshape(C, C).T + bo
+    wcat, bcat = fold_tail_weights(w2, b2, wo, bo)
+    assert wcat.shape == (C, 5 * C)
+    out = x + torch.cat([h, gate], 1) @ wcat.T + bcat
+    assert (out - ref).abs().max() < 1e-12
+
+
+def test_attention_head_stride(monkeypatch):
+    """unet._dpad: the narrowest stride the attention kernels accept (a multiple of 8, >= 16*ceil(d/16), room for the
+    ones column at index d); whole slabs with B200AD_TIGHT_HEADS=0; none in the fp32 mode."""
+    from types import SimpleNamespace
+    from b200ad.unet import _dpad
+    bf, f32 = SimpleNamespace(mode="bf16"), SimpleNamespace(mode="fp32")
+    monkeypatch.delenv("B200AD_TIGHT_HEADS", raising=False)
+    assert [_dpad(d, bf) for d in (40, 80, 160, 64, 8)] == [48, 88, 168, 64, 16]
+    assert _dpad(40, f32) == 40
+    for d in (8, 24, 40, 64, 80, 160):
+        p = _dpad(d, bf)
+        assert p % 8 == 0 and p >= 16 * ((d + 15) // 16) and (p > d or p in (64, 128, 192))
+    monkeypatch.setenv("B200AD_TIGHT_HEADS", "0")
+    assert [_dpad(d, bf) for d in (40, 80, 160)] == [64, 128, 192]
+    with pytest.raises(ValueError):
+        _dpad(200, bf)

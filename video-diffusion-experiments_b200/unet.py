@@ -367,9 +367,15 @@ def _fold_tail(o: Ops, ff: "FeedForward", w_out: torch.Tensor, b_out: torch.Tens
     B200AD_FOLD_TAIL=0 turns it off."""
     if o.mode != "bf16" or os.environ.get("B200AD_FOLD_TAIL", "1") == "0":
         return None, None
-    w2, b2 = ff.net[2].weight.detach().double(), ff.net[2].bias.detach().double()
+    wcat, bcat = fold_tail_weights(ff.net[2].weight, ff.net[2].bias, w_out, b_out)
+    return _dev_w(o, wcat), _dev_f(bcat)
+
+
+def fold_tail_weights(w2, b2, w_out, b_out):
+    """fp64 ([Wout | Wout W2] of shape [C, 5C], Wout b2 + bout) -- the algebra of _fold_tail (host side, any device)."""
+    w2, b2 = w2.detach().double(), b2.detach().double()
     wo, bo = w_out.detach().double().reshape(w_out.shape[0], -1), b_out.detach().double()
-    return _dev_w(o, torch.cat([wo, wo @ w2], 1)), _dev_f(wo @ b2 + bo)
+    return torch.cat([wo, wo @ w2], 1), wo @ b2 + bo
 
 
 class Transformer2DModel(_Packable):
@@ -486,6 +492,11 @@ def _pack_upconv3x3(o: Ops, w: torch.Tensor) -> torch.Tensor:
     image sees a 2x2 convolution of the low-resolution image whose tap (ty, tx) is the sum of the 3x3 weights that land
     on source pixel (y + ty - 1 + py, x + tx - 1 + px): rows ky with floor((py + ky - 1) / 2) == ty - 1 + py.
     Summed in fp64, rounded to the operand type once; k = (ty*2 + tx)*cin + c."""
+    return _dev_w(o, upconv_weights(w))
+
+
+def upconv_weights(w: torch.Tensor) -> torch.Tensor:
+    """fp64 [4, cout, 4*cin] sub-pixel weights of a [cout, cin, 3, 3] convolution (host side, any device)."""
     wd = w.detach().double()
     cout, cin = wd.shape[:2]
     rows = {0: ((0,), (1, 2)), 1: ((0, 1), (2,))}      # phase -> (ky of tap 0, ky of tap 1)
@@ -497,7 +508,7 @@ def _pack_upconv3x3(o: Ops, w: torch.Tensor) -> torch.Tensor:
                     for ky in rows[py][ty]:
                         for kx in rows[px][tx]:
                             out[py * 2 + px, :, ty, tx] += wd[:, :, ky, kx]
-    return _dev_w(o, out.reshape(4, cout, 4 * cin))
+    return out.reshape(4, cout, 4 * cin)
 
 
 def _pack_conv3x3(o: Ops, w: torch.Tensor) -> torch.Tensor:
