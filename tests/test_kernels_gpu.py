@@ -432,7 +432,11 @@ def test_attention_lazy_rescale_with_growing_maxima(d, dpad):
 @pytest.mark.parametrize("mode,tol", MODES)
 @pytest.mark.parametrize("B,Fr,hw,C,heads", [(2, 16, 64, 320, 8), (1, 16, 16, 1280, 8), (2, 8, 9, 640, 8),
                                              (1, 32, 4, 1280, 8), (2, 4, 16, 64, 8), (1, 16, 5, 1280, 8),
-                                             (1, 20, 7, 320, 8)])
+                                             (1, 20, 7, 320, 8),
+                                             # the instantiated head widths (40 / 80 / 160) with one and two frame tiles,
+                                             # odd position counts, fewer heads, and a generic width with a half k-step
+                                             (2, 32, 8, 640, 8), (1, 24, 3, 320, 4), (3, 16, 33, 320, 8),
+                                             (1, 16, 10, 192, 8), (2, 16, 1024, 320, 8), (1, 12, 6, 1280, 8)])
 def test_temporal_attention(mode, tol, B, Fr, hw, C, heads):
     o = ops(mode)
     d = C // heads

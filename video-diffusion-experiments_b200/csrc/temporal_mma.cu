@@ -35,12 +35,27 @@ __device__ __forceinline__ void mma_bf16_16816(float* c, const uint32_t* a, uint
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-// FT = number of 16-row frame tiles (F <= 16*FT).
-template <int FT>
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_fast(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// FT = number of 16-row frame tiles (F <= 16*FT).  D = head width as a compile-time constant (40 / 80 / 160: the
+// k-step, n-tile and half-step logic unrolls and folds away) or 0 for the run-time value `d_rt`.  The kernel is
+// issue-bound (ncu: 86 % issue-active at 48 % DRAM, ~1040 warp instructions per (position, head)), so every loop
+// counter, select and slow-path math call (exp2f, IEEE division) removed is time.
+template <int FT, int D>
 __global__ void __launch_bounds__(256)
-temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int d, int hpb, int PB, int npos,
+temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int d_rt, int hpb, int PB, int npos,
                          float scale_log2, bf16* __restrict__ out) {
   pdl_enter();
+  const int d = D ? D : d_rt;
   extern __shared__ __align__(16) uint8_t tsm[];
   constexpr int FP = 16 * FT;
   const int W = hpb * d;                 // columns of this head group, per part
@@ -63,8 +78,30 @@ temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int
     out_base[threadIdx.x] = ((long long)b * F * hw + sp) * C + col0;
   }
   __syncthreads();
-  {
-    const int rowlen = 3 * cpp;                        // 16-byte chunks per smem row
+  const int rowlen = 3 * cpp;                          // 16-byte chunks per smem row
+  if ((int)blockDim.x >= rowlen) {
+    // every thread keeps ONE 16-byte column of the (q|k|v) row and walks down the rows, blockDim / rowlen rows per
+    // pass (the last blockDim % rowlen threads idle): part / chunk / addresses are computed once, the loop body is
+    // an add, a compare and the copy
+    const int nrows = PB * FP;
+    const int drow = (int)blockDim.x / rowlen;
+    int row = (int)threadIdx.x / rowlen;
+    const int col = (int)threadIdx.x - row * rowlen;
+    if (row < drow) {
+      const int part = (col >= cpp) + (col >= 2 * cpp);
+      const int ch = col - part * cpp;
+      const int soff = part * W + ch * 8;              // element offset inside an smem row
+      const int goff = part * C + ch * 8;              // element offset inside a global (q|k|v) row
+      const long long fstride = (long long)hw * C3;
+      for (; row < nrows; row += drow) {
+        const int f = row & (FP - 1), pp = row / FP;
+        bf16* dst = sm + (size_t)row * RS + soff;
+        const long long pb = pos_base[pp];
+        if (f < F && pb >= 0) cp_async16(dst, qkv + pb + f * fstride + goff);
+        else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+  } else {
     const int nrows = PB * FP;
     const int dcol = (int)blockDim.x % rowlen, drow = (int)blockDim.x / rowlen;
     int row = (int)threadIdx.x / rowlen, col = (int)threadIdx.x - row * rowlen;
@@ -100,10 +137,11 @@ temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int
       for (int nt = 0; nt < 2 * FT; ++nt)
 #pragma unroll
         for (int i = 0; i < 4; ++i) S[mt][nt][i] = 0.f;
-    const int ksteps = (d + 15) >> 4;
+    const int ksteps = (d + 15) >> 4;                 // compile-time when D != 0
     const uint32_t a_off = (uint32_t)(((lane & 15) * RS + (lane >> 4) * 8) * 2);
     const uint32_t b_off = (uint32_t)((((lane & 7) + ((lane >> 4) << 3)) * RS + ((lane >> 3) & 1) * 8) * 2);
-    for (int ks = 0; ks < ksteps; ++ks) {
+#pragma unroll
+    for (int ks = 0; ks < (D ? (D + 15) / 16 : ksteps); ++ks) {
       const bool half = (ks * 16 + 8 >= d);           // only columns [16ks, 16ks+8) belong to this head
       uint32_t a[FT][4];
 #pragma unroll
@@ -134,7 +172,7 @@ temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int col = nt * 8 + 2 * t + (i & 1);
-          if (col >= F) S[mt][nt][i] = -INFINITY;
+          if (F < FP && col >= F) S[mt][nt][i] = -INFINITY;
           if (i < 2) mx0 = fmaxf(mx0, S[mt][nt][i]); else mx1 = fmaxf(mx1, S[mt][nt][i]);
         }
       mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
@@ -145,8 +183,9 @@ temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int
       float l0 = 0.f, l1 = 0.f;
 #pragma unroll
       for (int nt = 0; nt < 2 * FT; ++nt) {
-        const float p0 = exp2f(S[mt][nt][0] * scale_log2 - o0), p1 = exp2f(S[mt][nt][1] * scale_log2 - o0);
-        const float p2 = exp2f(S[mt][nt][2] * scale_log2 - o1), p3 = exp2f(S[mt][nt][3] * scale_log2 - o1);
+        // arguments are <= 0 (the row maximum is subtracted); -inf (masked column) -> 0
+        const float p0 = ex2_fast(S[mt][nt][0] * scale_log2 - o0), p1 = ex2_fast(S[mt][nt][1] * scale_log2 - o0);
+        const float p2 = ex2_fast(S[mt][nt][2] * scale_log2 - o1), p3 = ex2_fast(S[mt][nt][3] * scale_log2 - o1);
         l0 += p0 + p1;
         l1 += p2 + p3;
         P[mt][nt >> 1][(nt & 1) * 2 + 0] = pack_bf16x2(p0, p1);
@@ -156,15 +195,16 @@ temporal_attn_mma_kernel(const bf16* __restrict__ qkv, int F, int hw, int C, int
       l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
       l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
       l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-      inv_l[mt][0] = 1.f / l0;
-      inv_l[mt][1] = 1.f / l1;
+      inv_l[mt][0] = rcp_fast(l0);                  // l >= 1 (the maximum's own term)
+      inv_l[mt][1] = rcp_fast(l1);
     }
     __syncwarp();                                     // every lane's Q fragments are loaded: the Q slot may be reused
     // ---- O = P V, two 8-column n-tiles at a time; results go to this warp's own (dead) Q slot in smem
     const uint32_t v_off = (uint32_t)((((lane & 7) + ((lane >> 3) & 1) * 8) * RS + (lane >> 4) * 8) * 2);
     bf16* o_s = base + hl * d;
     const int ntiles = d >> 3;
-    for (int n0 = 0; n0 < ntiles; n0 += 2) {
+#pragma unroll
+    for (int n0 = 0; n0 < (D ? D / 8 : ntiles); n0 += 2) {
       const bool pair = (n0 + 1 < ntiles);
       float O[FT][2][4];
 #pragma unroll
@@ -232,18 +272,23 @@ int temporal_attention_bf16_mma(const bf16* qkv, int B, int F, int hw, int C, in
   B200AD_REQUIRE(smem <= 200 * 1024, "temporal_attention: needs %zu bytes of shared memory", smem);
   static bool attr_set = false;
   if (!attr_set) {
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(temporal_attn_mma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    B200AD_CHECK_CUDA(cudaFuncSetAttribute(temporal_attn_mma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+#define TA_ATTR(FTV, DV) B200AD_CHECK_CUDA((cudaFuncSetAttribute(temporal_attn_mma_kernel<FTV, DV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)))
+    TA_ATTR(1, 0); TA_ATTR(2, 0); TA_ATTR(1, 40); TA_ATTR(1, 80); TA_ATTR(1, 160); TA_ATTR(2, 40); TA_ATTR(2, 80); TA_ATTR(2, 160);
+#undef TA_ATTR
     attr_set = true;
   }
   const int npos = B * hw;
   const int threads = 32 * PB * hpb;
   dim3 grid((npos + PB - 1) / PB, heads / hpb);
   const float sl2 = 1.4426950408889634f / sqrtf((float)d);
-  if (FT == 1)
-    pdl_launch(temporal_attn_mma_kernel<1>, dim3(grid), dim3(threads), (size_t)(smem), (cudaStream_t)(st), qkv, F, hw, C, d, hpb, PB, npos, sl2, out);
-  else
-    pdl_launch(temporal_attn_mma_kernel<2>, dim3(grid), dim3(threads), (size_t)(smem), (cudaStream_t)(st), qkv, F, hw, C, d, hpb, PB, npos, sl2, out);
+#define TA_LAUNCH(FTV, DV) pdl_launch(temporal_attn_mma_kernel<FTV, DV>, dim3(grid), dim3(threads), (size_t)(smem), (cudaStream_t)(st), qkv, F, hw, C, d, hpb, PB, npos, sl2, out)
+  // the UNet's head widths (SD1.5 motion modules: 320 / 640 / 1280 channels over 8 heads) get their own instantiation
+  if (FT == 1) {
+    if (d == 40) TA_LAUNCH(1, 40); else if (d == 80) TA_LAUNCH(1, 80); else if (d == 160) TA_LAUNCH(1, 160); else TA_LAUNCH(1, 0);
+  } else {
+    if (d == 40) TA_LAUNCH(2, 40); else if (d == 80) TA_LAUNCH(2, 80); else if (d == 160) TA_LAUNCH(2, 160); else TA_LAUNCH(2, 0);
+  }
+#undef TA_LAUNCH
   count_launch();
   B200AD_CHECK_CUDA(cudaGetLastError());
   return 0;
