@@ -109,6 +109,55 @@ def conv():
                src.numel() * 2 + w.numel() * 2 + 4.0 * n * r * r * cout)
 
 
+def restructured():
+    """The restructured convolutions of DESIGN 3.11 against the module-order forms they replace."""
+    from b200ad.unet import _pack_upconv3x3
+    # Upsample2D of the UNet's up blocks 0 / 1 / 2 (source resolution 8 / 16 / 32 at 16f 512^2)
+    for n, c, r in [(32, 1280, 8), (32, 1280, 16), (32, 640, 32)]:
+        x = torch.randn(n * r * r, c, device="cuda")
+        wt = torch.randn(c, c, 3, 3) * (9 * c) ** -0.5
+        w9 = wt.permute(0, 2, 3, 1).reshape(c, -1).to("cuda", torch.bfloat16).contiguous()
+        w4 = _pack_upconv3x3(o, wt)
+        bias = torch.randn(c, device="cuda")
+        us0 = timeit(lambda: o.conv3x3(o.cast(x, n, r, r, c, mode=2), w9, n, 2 * r, 2 * r, bias=bias, stats=True), 5)
+        us1 = timeit(lambda: o.upconv3x3(o.cast(x, n, r, r, c), w4, n, r, r, bias=bias, stats=True), 5)
+        fl = 2.0 * n * 4 * r * r * c * 9 * c
+        report(f"upsample x2 + conv3x3 n={n} C={c} @{r}->{2 * r}: cast(mode 2) + conv", us0, fl, 0)
+        report(f"    sub-pixel: cast + 4 x (2x2 conv) [4/9 of the MACs]", us1, fl * 4 / 9, 0)
+    # ResnetBlock2D.conv2 + conv_shortcut of the up blocks (cin = skip concat)
+    for n, cin, cout, r in [(32, 960, 320, 64), (32, 640, 320, 64), (32, 1920, 640, 32), (32, 2560, 1280, 16),
+                            (32, 2560, 1280, 8)]:
+        a2, raw = bf(n * r * r, cout), bf(n * r * r, cin)
+        w2, wsc = bf(cout, 9 * cout, scale=(9 * cout) ** -0.5), bf(cout, cin, scale=cin ** -0.5)
+        wcat = torch.cat([w2, wsc], 1).contiguous()
+        bias = torch.randn(cout, device="cuda")
+
+        def two():
+            res, _ = o.gemm(raw, wsc, bias=bias, want_f32=True)
+            o.conv3x3(a2, w2, n, r, r, bias=bias, residual=res, stats=True)
+        us0 = timeit(two, 5)
+        us1 = timeit(lambda: o.conv3x3_sc(a2, wcat, raw, n, r, r, bias=bias, stats=True), 5)
+        fl = 2.0 * n * r * r * cout * (9 * cout + cin)
+        report(f"conv2 + shortcut n={n} {cout}(+{cin} sc) @{r}: gemm + conv", us0, fl, 0)
+        report(f"    one launch (second K segment)", us1, fl, 0)
+    # last block's FF2 + proj_out: two GEMMs against the folded K = 5C GEMM (+ the operand copy in attn2's out-projection)
+    for hw, C in [(4096, 320), (1024, 640), (256, 1280), (64, 1280)]:
+        M = 32 * hw
+        g, h, x = bf(M, 4 * C), torch.randn(M, C, device="cuda"), torch.randn(M, C, device="cuda")
+        w2, wo = bf(C, 4 * C, scale=(4 * C) ** -0.5), bf(C, C, scale=C ** -0.5)
+        cat, wcat = bf(M, 5 * C), bf(C, 5 * C, scale=(5 * C) ** -0.5)
+        bias = torch.randn(C, device="cuda")
+
+        def two():
+            hb = o.gemm(g, w2, bias=bias, residual=h, want_op=True)[1]
+            o.gemm(hb, wo, bias=bias, residual=x, out_f32=x, stats_hw=hw)
+        us0 = timeit(two, 5)
+        us1 = timeit(lambda: o.gemm(cat, wcat, bias=bias, residual=x, out_f32=x, stats_hw=hw), 5)
+        fl = 2.0 * M * C * 5 * C
+        report(f"FF2 + proj_out M={M} C={C}: two GEMMs", us0, fl, 0)
+        report(f"    folded K = 5C GEMM", us1, fl, 0)
+
+
 def norm():
     for hw, C in [(4096, 320), (1024, 640), (256, 1280)]:
         x = torch.randn(32 * hw, C, device="cuda")
@@ -130,6 +179,6 @@ def norm():
 
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
-    for name in ("temporal", "attention", "gemm", "conv", "norm"):
+    for name in ("temporal", "attention", "gemm", "conv", "norm", "restructured"):
         if which in (name, "all"):
             globals()[name]()
