@@ -108,8 +108,9 @@ int b200ad_conv3x3_sc(int op_dtype, const void* src, const void* W, int nimg, in
  * source, one per output phase (py, px).  src: operand-typed NHWC [nimg, h, w, cin]; outputs are rows of the
  * [nimg, 2h, 2w] image.  W4: [4 phases (py*2+px)][cout][2x2 taps (ty*2+tx)][cin] where tap (ty, tx) of phase (py, px) is
  * the sum of the 3x3 weights w[ky][kx] with floor((py + ky - 1) / 2) == ty - 1 + py (same in x), reading source pixel
- * (y + ty - 1 + py, x + tx - 1 + px).  bf16 (tcgen05) path only.  col_stats (optional, fp32-only output): as
- * b200ad_conv3x3_stats, 4 * b200ad_stats_slots(1, h, w) slots per image. */
+ * (y + ty - 1 + py, x + tx - 1 + px).  One launch over (phase, pixel tile, column tile).  bf16 (tcgen05) path only;
+ * fp32 output (out_op / ld_oop are reserved: pass NULL / 0).  col_stats (optional): as b200ad_conv3x3_stats,
+ * 4 * b200ad_stats_slots(1, h, w) slots per image. */
 int b200ad_upconv3x3(int op_dtype, const void* src, const void* W4, int nimg, int h, int w, int cin, int cout,
                      const float* bias, float* out_f32, long long ld_o32, void* out_op, long long ld_oop,
                      float* col_stats, void* stream);

@@ -19,6 +19,8 @@ struct ConvGeom {
   // this launch is pixel (n, out_scale*y + out_py, out_scale*x + out_px) of an [nimg, out_scale*h, out_scale*w] image.
   // out_scale = 0 or 1: plain output.  Applies to out_f32 / out_op / residual alike (tcgen05 path only).
   int out_scale, out_py, out_px;
+  int nphase;                  // 4: all four sub-pixel phases in ONE launch (W = [4][N][K] stacked, taps of phase (0,0)
+                               // shifted by (py, px) per phase, out_py/out_px ignored); 0 / 1: the single phase above
   // Second K segment (a 1x1 convolution accumulated into the same tile: ResnetBlock2D.conv2 + conv_shortcut): after the
   // ntaps*cin columns of the taps, K continues with sc_cin channels of `sc_src` [nimg, h, w, sc_cin] (operand-typed,
   // output geometry, no shift).  W is [N, ntaps*cin + sc_cin].  tcgen05 path only.

@@ -53,6 +53,8 @@ struct TcParams {
   int tiles_x, tiles_y;
   int cin_blocks;
   int kb_main;                 // conv: k-blocks that come from the taps; the rest (if any) from EpiMaps::a2
+  int nphase;                  // conv: 1, or 4 sub-pixel output phases in one launch (tile = (phase, m pair, n tile))
+  int slots_per_phase;         // conv statistics: slots one phase fills per image (tiles per image)
   int tap_dy[9], tap_dx[9], tap_dn[9];
   // epilogue
   int has_res, has_o32, has_oop, geglu;
@@ -149,9 +151,16 @@ __host__ __device__ __forceinline__ uint32_t umma_idesc_m(uint32_t m, uint32_t n
 struct TileCoord {
   int m_tile, n_tile;
   int x0, y0, n0;
+  int ph;                      // sub-pixel phase py*2 + px (0 unless TcParams::nphase == 4)
 };
 __device__ __forceinline__ TileCoord tile_coord(const TcParams& p, int tile, int rank) {
   TileCoord t;
+  t.ph = 0;
+  if (p.nphase > 1) {
+    const int per_phase = p.num_m_pairs * p.num_n_tiles;
+    t.ph = tile / per_phase;
+    tile -= t.ph * per_phase;
+  }
   t.n_tile = tile % p.num_n_tiles;
   t.m_tile = (tile / p.num_n_tiles) * 2 + rank;
   t.x0 = t.y0 = t.n0 = 0;
@@ -211,6 +220,7 @@ __device__ __forceinline__ void sts_u4(uint32_t a, uint32_t x, uint32_t y, uint3
 struct EpiMaps {
   CUtensorMap res, o32, oop;
   CUtensorMap a2;              // conv: source of the second K segment (ConvGeom::sc_src)
+  CUtensorMap o32p[3];         // fp32 output maps of sub-pixel phases 1..3 (phase 0 uses o32)
 };
 
 // Elected epilogue thread: make chunk buffer `buf` of group `g` ready for chunk `cur` (fetch its residual, or
@@ -298,7 +308,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int rank = (int)cluster_ctarank();
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
-  const int num_tiles = p.num_m_pairs * p.num_n_tiles;
+  const int num_tiles = p.num_m_pairs * p.num_n_tiles * p.nphase;
   const uint32_t tmem_cols = (2 * p.BN <= 256) ? 256u : 512u;
 
   if (warp == 0 && lane == 0) {
@@ -308,6 +318,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (f_o32) tma_prefetch_desc(&em.o32);
     if (f_oop) tma_prefetch_desc(&em.oop);
     if (p.conv && p.kb_main < p.num_kb) tma_prefetch_desc(&em.a2);
+    if (p.nphase > 1)
+      for (int i = 0; i < 3; ++i) tma_prefetch_desc(&em.o32p[i]);
     for (int s = 0; s < p.num_stages; ++s) {
       mbar_init(&full_bar[s], 2);        // the leader's A producer and W producer each arrive with their tx bytes
       mbar_init(&empty_bar[s], 1);
@@ -355,8 +367,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2u * A_STAGE_BYTES);
             if (p.conv) {
               if (kb < p.kb_main)
-                tma2_load_4d(sa, &tmA, fb0 + 8u * stage, cb * BK, t.x0 + p.tap_dx[tap], t.y0 + p.tap_dy[tap],
-                             t.n0 + p.tap_dn[tap]);
+                tma2_load_4d(sa, &tmA, fb0 + 8u * stage, cb * BK, t.x0 + p.tap_dx[tap] + (t.ph & 1),
+                             t.y0 + p.tap_dy[tap] + (t.ph >> 1), t.n0 + p.tap_dn[tap]);
               else
                 tma2_load_4d(sa, &em.a2, fb0 + 8u * stage, (kb - p.kb_main) * BK, t.x0, t.y0, t.n0);
             } else
@@ -383,7 +395,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       long long t_wait = 0;
       const long long t_begin = prof_clock();
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-        const int n_row = (tile % p.num_n_tiles) * p.BN + rank * half_bn;
+        const TileCoord tw = tile_coord(p, tile, rank);
+        const int n_row = tw.ph * p.N + tw.n_tile * p.BN + rank * half_bn;     // phase weights are stacked on the rows
         for (int kb = 0; kb < p.num_kb; ++kb) {
           const long long w0 = prof_clock();
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -475,7 +488,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (j * st_mq >= 4) continue;
           if (p.conv) {
             const int img = t.n0 + j;
-            if (img < p.nimg) st_off[j] = ((long long)img * p.stats_spi + p.stats_slot0 + (t.m_tile % (p.tiles_x * p.tiles_y))) * p.N;
+            if (img < p.nimg) st_off[j] = ((long long)img * p.stats_spi + p.stats_slot0 + t.ph * p.slots_per_phase + (t.m_tile % (p.tiles_x * p.tiles_y))) * p.N;
           } else {
             const long long row0 = (long long)t.m_tile * BM + j * 32 * st_mq;
             if (row0 < p.M) st_off[j] = (row0 / (32 * st_mq)) * p.N;
@@ -494,7 +507,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           uint8_t* ob = G.op + (size_t)G.buf * OP_BUF_BYTES;
           const int ocol = ocol0 + c * 32;
           if (p.conv) {
-            if (f_o32) tma_store_4d(&em.o32, fb, ocol, t.x0, t.y0, t.n0);
+            if (f_o32) tma_store_4d(t.ph == 0 ? &em.o32 : &em.o32p[t.ph - 1], fb, ocol, t.x0, t.y0, t.n0);
             if (f_oop) tma_store_4d(&em.oop, ob, ocol, t.x0, t.y0, t.n0);
           } else {
             if (f_o32) tma_store_2d(&em.o32, fb, ocol, t.m_tile * BM);
@@ -745,8 +758,10 @@ static int pick_bn(int N, long long m_pairs, int num_clusters, bool geglu) {
 }
 
 // Output / residual tensor map: dense [M, ld] rows, or the NHWC pixel box of a conv tile.  `elem` = 4 (fp32) or 2.
-static int make_out_map(CUtensorMap* tm, const void* ptr, long long ld, int ncols, int elem, const GemmArgs& a) {
-  const ConvGeom& g = a.conv;
+static int make_out_map(CUtensorMap* tm, const void* ptr, long long ld, int ncols, int elem, const GemmArgs& a,
+                        int phase = -1) {
+  ConvGeom g = a.conv;
+  if (phase >= 0) { g.out_py = phase >> 1; g.out_px = phase & 1; }
   const CUtensorMapDataType dt = elem == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   const CUtensorMapSwizzle sw = elem == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   if (g.enabled) {
@@ -815,6 +830,11 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     num_m_tiles = p.tiles_x * p.tiles_y * ((g.nimg + g.n_box - 1) / g.n_box);
     p.cin_blocks = g.cin / BK;
     p.kb_main = g.ntaps * p.cin_blocks;
+    if (g.nphase == 4) {
+      B200AD_REQUIRE(g.out_scale == 2 && !e.residual && !e.out_op && e.out_f32 && g.sc_cin == 0,
+                     "conv: the four-phase launch writes an fp32 output only (no residual / operand copy / second K segment)");
+      p.nphase = 4;
+    }
     if (g.sc_cin > 0) {
       uint64_t d2[4] = {(uint64_t)g.sc_cin, (uint64_t)g.w, (uint64_t)g.h, (uint64_t)g.nimg};
       uint64_t s2[3] = {(uint64_t)g.sc_cin * 2, (uint64_t)g.w * g.sc_cin * 2, (uint64_t)g.h * g.w * g.sc_cin * 2};
@@ -841,7 +861,8 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
                      g.n_box, g.h_box, g.w_box);
       p.stats_spi = g.stats_slots > 0 ? g.stats_slots : p.tiles_x * p.tiles_y;
       p.stats_slot0 = g.stats_slot0;
-      B200AD_REQUIRE(p.stats_slot0 >= 0 && p.stats_slot0 + p.tiles_x * p.tiles_y <= p.stats_spi,
+      p.slots_per_phase = p.tiles_x * p.tiles_y;
+      B200AD_REQUIRE(p.stats_slot0 >= 0 && p.stats_slot0 + (g.nphase == 4 ? 4 : 1) * p.tiles_x * p.tiles_y <= p.stats_spi,
                      "conv: statistic slots %d + %d beyond %d", p.stats_slot0, p.tiles_x * p.tiles_y, p.stats_spi);
     } else {
       B200AD_REQUIRE(e.stats_hw > 0 && e.stats_hw % 32 == 0 && a.M % e.stats_hw == 0,
@@ -851,20 +872,24 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     }
   }
   p.num_m_pairs = (num_m_tiles + 1) / 2;
+  if (p.nphase == 0) p.nphase = 1;
   const int max_clusters = g_num_sms / 2;
-  p.BN = pick_bn(a.N, p.num_m_pairs, max_clusters, e.geglu != 0);
+  p.BN = pick_bn(a.N, (long long)p.num_m_pairs * p.nphase, max_clusters, e.geglu != 0);
   p.num_n_tiles = (a.N + p.BN - 1) / p.BN;
   p.num_kb = (a.K + BK - 1) / BK;
   p.stage_bytes = A_STAGE_BYTES + (p.BN / 2) * BK * 2;
   {
-    uint64_t dims[2] = {(uint64_t)a.K, (uint64_t)a.N};
+    uint64_t dims[2] = {(uint64_t)a.K, (uint64_t)a.N * p.nphase};      // phase weights stacked on the rows
     uint64_t strides[1] = {(uint64_t)a.K * 2};
     uint32_t box[2] = {(uint32_t)BK, (uint32_t)(p.BN / 2)};
     if (int rc = make_tmap_bf16(&tmB, a.W, 2, dims, strides, box)) return rc;
   }
   const int n_out = e.geglu ? a.N / 2 : a.N;
   if (p.has_res) if (int rc = make_out_map(&em.res, e.residual, e.ld_res, n_out, 4, a)) return rc;
-  if (p.has_o32) if (int rc = make_out_map(&em.o32, e.out_f32, e.ld_o32, n_out, 4, a)) return rc;
+  if (p.has_o32) if (int rc = make_out_map(&em.o32, e.out_f32, e.ld_o32, n_out, 4, a, p.nphase == 4 ? 0 : -1)) return rc;
+  if (p.nphase == 4)
+    for (int ph = 1; ph < 4; ++ph)
+      if (int rc = make_out_map(&em.o32p[ph - 1], e.out_f32, e.ld_o32, n_out, 4, a, ph)) return rc;
   if (p.has_oop) if (int rc = make_out_map(&em.oop, e.out_op, e.ld_oop, n_out, 2, a)) return rc;
   // ---- shared memory plan: mainloop stages first, the rest goes to epilogue chunk buffers (bytes in flight)
   const int per_buf = ((p.has_res || p.has_o32) ? F32_BUF_BYTES : 0) + (p.has_oop ? OP_BUF_BYTES : 0);
@@ -920,7 +945,7 @@ int gemm_bf16_tc(const GemmArgs& a, cudaStream_t stream) {
     B200AD_CHECK_CUDA((cudaFuncSetAttribute(gemm_tc_kernel<6, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT)));
     g_attr_set = true;
   }
-  const long long tiles = (long long)p.num_m_pairs * p.num_n_tiles;
+  const long long tiles = (long long)p.num_m_pairs * p.num_n_tiles * p.nphase;
   const int clusters = (int)(tiles < max_clusters ? tiles : max_clusters);
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));

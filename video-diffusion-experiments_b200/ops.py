@@ -229,7 +229,7 @@ class Ops:
         out = _empty((M, cout), src.device, torch.float32)
         spi = self._stats_ok(True, h, wd) if stats else 0
         st = _empty((nimg * 4 * spi, cout, 2), src.device, torch.float32) if spi else None
-        with self._rec("conv3x3", 2.0 * M * cout * k4, _nb(src, w4, out, st), launches=4):
+        with self._rec("conv3x3", 2.0 * M * cout * k4, _nb(src, w4, out, st)):
             rc = self.L.b200ad_upconv3x3(self.op, src.data_ptr(), w4.data_ptr(), nimg, h, wd, cin, cout, _ptr(bias),
                                          out.data_ptr(), cout, None, 0, _ptr(st), _stream())
         _lib.check(rc, "b200ad_upconv3x3")
